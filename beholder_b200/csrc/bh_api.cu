@@ -1,0 +1,609 @@
+// bh_api.cu — the C-ABI of libbeholder_gpu.so (include/beholder_gpu.h): context, pinned ingest
+// ring, read side.  Host code only; kernels are in bh_kernels.cu.
+#include <stdarg.h>
+#include <stdio.h>
+#include <stdlib.h>
+
+#include <algorithm>
+#include <string>
+#include <vector>
+
+#include "bh_kernels.cuh"
+
+using namespace bh;
+
+namespace {
+
+thread_local std::string g_create_error;
+
+struct Slab {
+  uint8_t* h_payload = nullptr;
+  uint32_t* h_offsets = nullptr;
+  uint64_t* h_ts = nullptr;
+  uint8_t* d_payload = nullptr;
+  uint32_t* d_offsets = nullptr;
+  uint64_t* d_ts = nullptr;
+  uint32_t n = 0;
+  uint64_t bytes = 0;
+  bool any_ts = false;
+  bool in_flight = false;
+  uint64_t seq_end = 0;
+  cudaEvent_t copied = nullptr, done = nullptr;
+};
+
+}  // namespace
+
+struct bh_ctx {
+  bh_config cfg;
+  int device = 0;
+  DevSchema S;
+  DevTables T;
+  LaunchGeom G;
+  cudaStream_t st_compute = nullptr;
+  cudaStream_t st_copy[2] = {nullptr, nullptr};
+  std::vector<Slab> slabs;
+  uint32_t cur = 0;
+  uint64_t slab_bytes = 0;
+  uint32_t slab_events = 0;
+  uint64_t pushed = 0, committed = 0;
+  unsigned long long* d_owner_counts = nullptr;   // [1024]
+  unsigned long long* d_owner_cursor = nullptr;   // [1024]
+  bh_record* d_export = nullptr;
+  uint32_t* d_export_hist = nullptr;
+  uint64_t export_cap = 0;
+  unsigned long long* h_small = nullptr;          // pinned, 1024 u64
+  int launches = 0;
+  std::string err;
+};
+
+namespace {
+
+int fail(bh_ctx* c, int code, const char* fmt, ...) {
+  char buf[512];
+  va_list ap; va_start(ap, fmt); vsnprintf(buf, sizeof buf, fmt, ap); va_end(ap);
+  if (c) c->err = buf; else g_create_error = buf;
+  return code;
+}
+
+#define CU(c, call)                                                                                \
+  do {                                                                                             \
+    cudaError_t e__ = (call);                                                                      \
+    if (e__ != cudaSuccess) return fail((c), BH_ERR_CUDA, "%s: %s", #call, cudaGetErrorString(e__)); \
+  } while (0)
+
+bool is_pow2(uint64_t v) { return v && !(v & (v - 1)); }
+
+int build_schema(const bh_config& cfg, DevSchema& S) {
+  memset(&S, 0, sizeof S);
+  uint32_t parts = 0;
+  bool have_status = false;
+  for (uint32_t i = 0; i < cfg.n_fields; i++) {
+    const bh_field& f = cfg.fields[i];
+    if (f.number < 1 || f.number > BH_MAX_FIELD_NUMBER) return fail(nullptr, BH_ERR_UNSUPPORTED, "field number %u outside 1..%d", f.number, BH_MAX_FIELD_NUMBER);
+    if (f.kind < BH_K_STRING || f.kind > BH_K_DOUBLE) return fail(nullptr, BH_ERR_UNSUPPORTED, "field %u: unsupported declared type %u", f.number, f.kind);
+    if (S.kind[f.number]) return fail(nullptr, BH_ERR_INVALID, "field %u declared twice", f.number);
+    S.kind[f.number] = (uint8_t)f.kind;
+    S.role[f.number] = (uint8_t)f.role;
+    bool is_len = f.kind == BH_K_STRING || f.kind == BH_K_BYTES;
+    if (f.role & BH_R_STATUS) {
+      if (is_len || f.kind >= BH_K_FLOAT) return fail(nullptr, BH_ERR_INVALID, "status field %u must be a 32-bit varint type", f.number);
+      have_status = true;
+    }
+    if ((f.role & BH_R_VALUE) && is_len) return fail(nullptr, BH_ERR_INVALID, "value field %u must be numeric", f.number);
+    if (f.role & BH_R_KEY) {
+      if (f.kind == BH_K_FLOAT || f.kind == BH_K_DOUBLE) return fail(nullptr, BH_ERR_UNSUPPORTED, "key field %u: float keys not supported", f.number);
+      if (parts >= BH_MAX_KEY_PARTS) return fail(nullptr, BH_ERR_UNSUPPORTED, "more than %d key fields", BH_MAX_KEY_PARTS);
+      S.part[f.number] = (uint8_t)(parts + 1);
+      S.part_field[parts] = (uint8_t)f.number;
+      S.part_is_len[parts] = is_len;
+      parts++;
+    }
+  }
+  S.n_parts = parts;
+  S.mode = cfg.mode;
+  if (cfg.mode == BH_MODE_REFERENCE) {
+    if (!have_status) return fail(nullptr, BH_ERR_INVALID, "REFERENCE mode needs a field with BH_R_STATUS");
+    S.status_part = 1;
+    S.ops = BH_OP_COUNT;
+  } else if (cfg.mode == BH_MODE_WINDOWED) {
+    S.ops = cfg.ops | BH_OP_COUNT;
+    S.identity_key = parts == 1 && !S.part_is_len[0];
+  } else {
+    return fail(nullptr, BH_ERR_INVALID, "unknown mode %u", cfg.mode);
+  }
+  if (cfg.n_enum > BH_MAX_ENUM) return fail(nullptr, BH_ERR_INVALID, "n_enum > %d", BH_MAX_ENUM);
+  for (uint32_t i = 0; i < cfg.n_enum; i++) {
+    if (cfg.enum_numbers[i] < 0 || cfg.enum_numbers[i] > 63) return fail(nullptr, BH_ERR_UNSUPPORTED, "enum number %d outside 0..63", cfg.enum_numbers[i]);
+    S.enum_mask |= 1ull << cfg.enum_numbers[i];
+  }
+  S.has_enum = cfg.n_enum > 0 && have_status;
+  S.hist_buckets = cfg.hist_buckets ? cfg.hist_buckets : BH_HIST_MAX;
+  if (S.hist_buckets < 2 || S.hist_buckets > BH_HIST_MAX) return fail(nullptr, BH_ERR_INVALID, "hist_buckets must be 2..%d", BH_HIST_MAX);
+  S.hist_e0 = cfg.hist_e0;
+  S.hash_seed = cfg.hash_seed;
+  S.has_window = cfg.mode == BH_MODE_WINDOWED && cfg.window_ms > 0;
+  if (S.has_window) S.wdiv = make_div64(cfg.window_ms);
+  return BH_OK;
+}
+
+int slab_alloc(bh_ctx* c, Slab& s) {
+  CU(c, cudaHostAlloc((void**)&s.h_payload, c->slab_bytes + 64, cudaHostAllocDefault));
+  CU(c, cudaHostAlloc((void**)&s.h_offsets, ((size_t)c->slab_events + 1) * 4, cudaHostAllocDefault));
+  CU(c, cudaHostAlloc((void**)&s.h_ts, (size_t)c->slab_events * 8, cudaHostAllocDefault));
+  CU(c, cudaMalloc((void**)&s.d_payload, c->slab_bytes + 64));
+  CU(c, cudaMalloc((void**)&s.d_offsets, ((size_t)c->slab_events + 1) * 4));
+  CU(c, cudaMalloc((void**)&s.d_ts, (size_t)c->slab_events * 8));
+  CU(c, cudaEventCreateWithFlags(&s.copied, cudaEventDisableTiming));
+  CU(c, cudaEventCreateWithFlags(&s.done, cudaEventDisableTiming));
+  s.h_offsets[0] = 0;
+  return BH_OK;
+}
+
+void slab_free(Slab& s) {
+  if (s.h_payload) cudaFreeHost(s.h_payload);
+  if (s.h_offsets) cudaFreeHost(s.h_offsets);
+  if (s.h_ts) cudaFreeHost(s.h_ts);
+  if (s.d_payload) cudaFree(s.d_payload);
+  if (s.d_offsets) cudaFree(s.d_offsets);
+  if (s.d_ts) cudaFree(s.d_ts);
+  if (s.copied) cudaEventDestroy(s.copied);
+  if (s.done) cudaEventDestroy(s.done);
+  s = Slab();
+}
+
+// wait until slab i is free for refilling
+int slab_acquire(bh_ctx* c, uint32_t i) {
+  Slab& s = c->slabs[i];
+  if (s.in_flight) {
+    CU(c, cudaEventSynchronize(s.done));
+    s.in_flight = false;
+    if (s.seq_end > c->committed) c->committed = s.seq_end;
+  }
+  return BH_OK;
+}
+
+// launch the fused kernel over what slab `s` holds on the device; `virt` is the payload base the
+// offsets are relative to
+int slab_launch(bh_ctx* c, Slab& s, const uint8_t* virt, uint32_t n, bool with_ts, cudaStream_t copy_stream) {
+  CU(c, cudaEventRecord(s.copied, copy_stream));
+  CU(c, cudaStreamWaitEvent(c->st_compute, s.copied, 0));
+  CU(c, launch_process_raw(c->S, c->T, c->G, virt, s.d_offsets, with_ts ? s.d_ts : nullptr, n, c->st_compute, &c->launches));
+  CU(c, cudaEventRecord(s.done, c->st_compute));
+  s.in_flight = true;
+  s.seq_end = c->pushed;
+  return BH_OK;
+}
+
+// submit the host-staged slab `cur`
+int submit_current(bh_ctx* c) {
+  Slab& s = c->slabs[c->cur];
+  if (s.n == 0) return BH_OK;
+  cudaStream_t cs = c->st_copy[c->cur & 1];
+  CU(c, cudaMemcpyAsync(s.d_payload, s.h_payload, (s.bytes + 15) & ~15ull, cudaMemcpyHostToDevice, cs));
+  CU(c, cudaMemcpyAsync(s.d_offsets, s.h_offsets, ((size_t)s.n + 1) * 4, cudaMemcpyHostToDevice, cs));
+  bool with_ts = c->S.has_window;
+  if (with_ts) CU(c, cudaMemcpyAsync(s.d_ts, s.h_ts, (size_t)s.n * 8, cudaMemcpyHostToDevice, cs));
+  int rc = slab_launch(c, s, s.d_payload, s.n, with_ts, cs);
+  if (rc) return rc;
+  s.n = 0; s.bytes = 0; s.h_offsets[0] = 0;
+  c->cur = (c->cur + 1) % (uint32_t)c->slabs.size();
+  return slab_acquire(c, c->cur);
+}
+
+struct DeviceGuard {
+  int prev = -1;
+  explicit DeviceGuard(int dev) { cudaGetDevice(&prev); if (prev != dev) cudaSetDevice(dev); else prev = -1; }
+  ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+};
+
+int counters_status(const bh_counters& k) {
+  if (k.dropped_table_full) return BH_ERR_TABLE_FULL;
+  if (k.dropped_window) return BH_ERR_WINDOW_RING;
+  return BH_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int bh_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+  int ok = 0;
+  for (int i = 0; i < n; i++) {
+    int major = 0;
+    if (cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, i) == cudaSuccess && major == 10) ok++;
+  }
+  return ok;
+}
+
+const char* bh_last_error(bh_ctx* ctx) { return ctx ? ctx->err.c_str() : g_create_error.c_str(); }
+
+int bh_create(const bh_config* cfg, bh_ctx** out) {
+  if (!cfg || !out) return fail(nullptr, BH_ERR_INVALID, "null argument");
+  *out = nullptr;
+  if (cfg->struct_size != sizeof(bh_config)) return fail(nullptr, BH_ERR_INVALID, "bh_config.struct_size %u != %zu", cfg->struct_size, sizeof(bh_config));
+  DevSchema S;
+  int rc = build_schema(*cfg, S);
+  if (rc) return rc;
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0) {
+    cudaGetLastError();
+    return fail(nullptr, BH_ERR_NO_DEVICE, "no CUDA device (%s); this library has no CPU path", e != cudaSuccess ? cudaGetErrorString(e) : "count 0");
+  }
+  if (cfg->device < 0 || cfg->device >= ndev) return fail(nullptr, BH_ERR_INVALID, "device %d out of range (0..%d)", cfg->device, ndev - 1);
+  cudaDeviceProp prop;
+  if ((e = cudaGetDeviceProperties(&prop, cfg->device)) != cudaSuccess) return fail(nullptr, BH_ERR_CUDA, "cudaGetDeviceProperties: %s", cudaGetErrorString(e));
+  if (prop.major != 10) return fail(nullptr, BH_ERR_NO_DEVICE, "device %d is sm_%d%d; this library is built for sm_100a only", cfg->device, prop.major, prop.minor);
+
+  uint64_t cap = cfg->table_capacity ? cfg->table_capacity : (cfg->mode == BH_MODE_REFERENCE ? 64 : (1ull << 16));
+  if (!is_pow2(cap) || cap < 64 || cap > (1ull << 30)) return fail(nullptr, BH_ERR_INVALID, "table_capacity must be a power of two in [64, 2^30]");
+  uint32_t ring = cfg->window_ring ? cfg->window_ring : (S.has_window ? 32 : 1);
+  if (!is_pow2(ring) || ring > 1024) return fail(nullptr, BH_ERR_INVALID, "window_ring must be a power of two <= 1024");
+
+  bh_ctx* c = new bh_ctx();
+  c->cfg = *cfg; c->device = cfg->device; c->S = S;
+  DeviceGuard guard(c->device);
+  auto bail = [&](int code) { std::string m = c->err; bh_destroy(c); g_create_error = m; return code; };
+#define CUB_(call) do { cudaError_t e__ = (call); if (e__ != cudaSuccess) { fail(c, BH_ERR_CUDA, "%s: %s", #call, cudaGetErrorString(e__)); return bail(e__ == cudaErrorMemoryAllocation ? BH_ERR_NOMEM : BH_ERR_CUDA); } } while (0)
+  c->G.sms = prop.multiProcessorCount;
+  c->G.smem_optin = (int)prop.sharedMemPerBlockOptin;
+  CUB_(cudaStreamCreateWithFlags(&c->st_compute, cudaStreamNonBlocking));
+  CUB_(cudaStreamCreateWithFlags(&c->st_copy[0], cudaStreamNonBlocking));
+  CUB_(cudaStreamCreateWithFlags(&c->st_copy[1], cudaStreamNonBlocking));
+  DevTables& T = c->T;
+  memset(&T, 0, sizeof T);
+  T.cap = cap; T.stride = cap + 2; T.ring = ring; T.hist_buckets = S.hist_buckets;
+  size_t rows = (size_t)ring * T.stride;
+  CUB_(cudaMalloc((void**)&T.ring_win, (size_t)ring * 8));
+  CUB_(cudaMalloc((void**)&T.keys, rows * 8));
+  CUB_(cudaMalloc((void**)&T.stats, rows * sizeof(Stat)));
+  if (S.ops & BH_OP_HIST) CUB_(cudaMalloc((void**)&T.hist, rows * S.hist_buckets * 4));
+  CUB_(cudaMalloc((void**)&T.counters, 8 * 8));
+  CUB_(cudaMalloc((void**)&c->d_owner_counts, 1024 * 8));
+  CUB_(cudaMalloc((void**)&c->d_owner_cursor, 1024 * 8));
+  CUB_(cudaHostAlloc((void**)&c->h_small, 1024 * 8, cudaHostAllocDefault));
+  CUB_(launch_init_tables(T, c->st_compute));
+  CUB_(configure_kernels(c->G));
+  c->slab_bytes = cfg->slab_bytes ? cfg->slab_bytes : (64ull << 20);
+  c->slab_events = cfg->slab_events ? cfg->slab_events : (1u << 20);
+  if (c->slab_bytes > 0xFFFFFF00ull) { fail(c, BH_ERR_INVALID, "slab_bytes must stay below 4 GiB (u32 offsets)"); return bail(BH_ERR_INVALID); }
+  uint32_t n_slabs = cfg->n_slabs ? cfg->n_slabs : 3;
+  c->slabs.resize(n_slabs);
+  for (auto& s : c->slabs) {
+    int r2 = slab_alloc(c, s);
+    if (r2) return bail(r2);
+  }
+  CUB_(cudaStreamSynchronize(c->st_compute));
+#undef CUB_
+  *out = c;
+  return BH_OK;
+}
+
+void bh_destroy(bh_ctx* c) {
+  if (!c) return;
+  DeviceGuard guard(c->device);
+  if (c->st_compute) cudaStreamSynchronize(c->st_compute);
+  for (auto& s : c->slabs) slab_free(s);
+  if (c->T.ring_win) cudaFree(c->T.ring_win);
+  if (c->T.keys) cudaFree(c->T.keys);
+  if (c->T.stats) cudaFree(c->T.stats);
+  if (c->T.hist) cudaFree(c->T.hist);
+  if (c->T.counters) cudaFree(c->T.counters);
+  if (c->d_owner_counts) cudaFree(c->d_owner_counts);
+  if (c->d_owner_cursor) cudaFree(c->d_owner_cursor);
+  if (c->d_export) cudaFree(c->d_export);
+  if (c->d_export_hist) cudaFree(c->d_export_hist);
+  if (c->h_small) cudaFreeHost(c->h_small);
+  for (auto& s : c->st_copy) if (s) cudaStreamDestroy(s);
+  if (c->st_compute) cudaStreamDestroy(c->st_compute);
+  delete c;
+}
+
+int bh_host_alloc(void** out, size_t bytes) {
+  if (!out) return BH_ERR_INVALID;
+  cudaError_t e = cudaHostAlloc(out, bytes, cudaHostAllocPortable);
+  if (e != cudaSuccess) { g_create_error = cudaGetErrorString(e); cudaGetLastError(); return e == cudaErrorMemoryAllocation ? BH_ERR_NOMEM : BH_ERR_CUDA; }
+  return BH_OK;
+}
+int bh_host_free(void* p) { return cudaFreeHost(p) == cudaSuccess ? BH_OK : BH_ERR_CUDA; }
+
+int bh_push(bh_ctx* c, const uint8_t* payload, uint32_t len, uint64_t ts_ms) {
+  if (!c || (!payload && len)) return fail(c, BH_ERR_INVALID, "null argument");
+  if ((uint64_t)len > c->slab_bytes) return fail(c, BH_ERR_TOO_LARGE, "message of %u bytes exceeds slab_bytes %llu", len, (unsigned long long)c->slab_bytes);
+  DeviceGuard guard(c->device);
+  Slab* s = &c->slabs[c->cur];
+  if (s->bytes + len > c->slab_bytes || s->n == c->slab_events) {
+    int rc = submit_current(c);
+    if (rc) return rc;
+    s = &c->slabs[c->cur];
+  }
+  memcpy(s->h_payload + s->bytes, payload, len);
+  s->h_ts[s->n] = ts_ms;
+  s->bytes += len;
+  s->n++;
+  s->h_offsets[s->n] = (uint32_t)s->bytes;
+  c->pushed++;
+  return BH_OK;
+}
+
+int bh_push_batch(bh_ctx* c, const uint8_t* slab, const uint32_t* off, const uint64_t* ts, uint32_t n) {
+  if (!c || (n && (!slab || !off))) return fail(c, BH_ERR_INVALID, "null argument");
+  DeviceGuard guard(c->device);
+  uint32_t i = 0;
+  while (i < n) {
+    Slab* s = &c->slabs[c->cur];
+    if (off[i + 1] < off[i]) return fail(c, BH_ERR_INVALID, "offsets not monotone at %u", i);
+    uint64_t len0 = off[i + 1] - off[i];
+    if (len0 > c->slab_bytes) return fail(c, BH_ERR_TOO_LARGE, "message %u of %llu bytes exceeds slab_bytes", i, (unsigned long long)len0);
+    if (s->bytes + len0 > c->slab_bytes || s->n == c->slab_events) {
+      int rc = submit_current(c);
+      if (rc) return rc;
+      continue;
+    }
+    // largest j with events [i, j) fitting the current slab
+    uint64_t room_b = c->slab_bytes - s->bytes;
+    uint32_t room_e = c->slab_events - s->n;
+    uint32_t hi = std::min<uint64_t>(n, (uint64_t)i + room_e);
+    uint32_t j = (uint32_t)(std::upper_bound(off + i, off + hi + 1, (uint64_t)off[i] + room_b,
+                                            [](uint64_t v, uint32_t o) { return v < o; }) - off) - 1;
+    if (j <= i) j = i + 1;
+    for (uint32_t k = i; k < j; k++)
+      if (off[k + 1] < off[k]) return fail(c, BH_ERR_INVALID, "offsets not monotone at %u", k);
+    uint64_t nb = off[j] - off[i];
+    memcpy(s->h_payload + s->bytes, slab + off[i], nb);
+    for (uint32_t k = i; k < j; k++) {
+      s->h_offsets[s->n + (k - i) + 1] = (uint32_t)(s->bytes + (off[k + 1] - off[i]));
+      s->h_ts[s->n + (k - i)] = ts ? ts[k] : 0;
+    }
+    s->bytes += nb;
+    s->n += j - i;
+    c->pushed += j - i;
+    i = j;
+  }
+  return BH_OK;
+}
+
+int bh_push_batch_pinned(bh_ctx* c, const uint8_t* slab, const uint32_t* off, const uint64_t* ts, uint32_t n) {
+  if (!c || (n && (!slab || !off))) return fail(c, BH_ERR_INVALID, "null argument");
+  if (c->S.has_window && !ts && n) return fail(c, BH_ERR_INVALID, "ts_ms required in windowed mode");
+  DeviceGuard guard(c->device);
+  // keep arrival order: anything staged through bh_push goes first
+  int rc = submit_current(c);
+  if (rc) return rc;
+  uint32_t i = 0;
+  while (i < n) {
+    rc = slab_acquire(c, c->cur);
+    if (rc) return rc;
+    Slab& s = c->slabs[c->cur];
+    uint32_t hi = (uint32_t)std::min<uint64_t>(n, (uint64_t)i + c->slab_events);
+    uint32_t j = (uint32_t)(std::upper_bound(off + i, off + hi + 1, (uint64_t)off[i] + c->slab_bytes,
+                                            [](uint64_t v, uint32_t o) { return v < o; }) - off) - 1;
+    if (j <= i) return fail(c, BH_ERR_TOO_LARGE, "message %u exceeds slab_bytes", i);
+    uint64_t nb = off[j] - off[i];
+    uint32_t head = off[i] & 15u;
+    cudaStream_t cs = c->st_copy[c->cur & 1];
+    CU(c, cudaMemcpyAsync(s.d_payload + head, slab + off[i], nb, cudaMemcpyHostToDevice, cs));
+    CU(c, cudaMemcpyAsync(s.d_offsets, off + i, ((size_t)(j - i) + 1) * 4, cudaMemcpyHostToDevice, cs));
+    bool with_ts = c->S.has_window;
+    if (with_ts) CU(c, cudaMemcpyAsync(s.d_ts, ts + i, (size_t)(j - i) * 8, cudaMemcpyHostToDevice, cs));
+    c->pushed += j - i;
+    // offsets stay absolute: hand the kernel the (16-byte aligned) address offset 0 would have
+    const uint8_t* virt = s.d_payload + head - off[i];
+    rc = slab_launch(c, s, virt, j - i, with_ts, cs);
+    if (rc) return rc;
+    c->cur = (c->cur + 1) % (uint32_t)c->slabs.size();
+    i = j;
+  }
+  return slab_acquire(c, c->cur);
+}
+
+int bh_push_columns(bh_ctx* c, const uint64_t* kh, const uint64_t* ts, const double* val, uint64_t n) {
+  if (!c || (n && !kh)) return fail(c, BH_ERR_INVALID, "null argument");
+  if (c->S.mode != BH_MODE_WINDOWED) return fail(c, BH_ERR_INVALID, "bh_push_columns needs BH_MODE_WINDOWED");
+  if (c->S.has_window && !ts && n) return fail(c, BH_ERR_INVALID, "ts_ms required in windowed mode");
+  DeviceGuard guard(c->device);
+  int rc = submit_current(c);
+  if (rc) return rc;
+  uint64_t per = std::min<uint64_t>(c->slab_bytes / 24, 0x7FFFFFFFull);
+  if (per == 0) return fail(c, BH_ERR_INVALID, "slab_bytes too small");
+  uint64_t i = 0;
+  Slab* last = nullptr;
+  while (i < n) {
+    rc = slab_acquire(c, c->cur);
+    if (rc) return rc;
+    Slab& s = c->slabs[c->cur];
+    uint64_t m = std::min(per, n - i);
+    uint64_t* d_kh = (uint64_t*)s.d_payload;
+    uint64_t* d_ts = d_kh + m;
+    double* d_val = (double*)(d_ts + m);
+    cudaStream_t cs = c->st_copy[c->cur & 1];
+    CU(c, cudaMemcpyAsync(d_kh, kh + i, m * 8, cudaMemcpyHostToDevice, cs));
+    if (c->S.has_window) CU(c, cudaMemcpyAsync(d_ts, ts + i, m * 8, cudaMemcpyHostToDevice, cs));
+    if (val) CU(c, cudaMemcpyAsync(d_val, val + i, m * 8, cudaMemcpyHostToDevice, cs));
+    CU(c, cudaEventRecord(s.copied, cs));
+    CU(c, cudaStreamWaitEvent(c->st_compute, s.copied, 0));
+    c->pushed += m;
+    CU(c, launch_process_columns(c->S, c->T, c->G, d_kh, d_ts, val ? d_val : nullptr, m, c->st_compute, &c->launches));
+    CU(c, cudaEventRecord(s.done, c->st_compute));
+    s.in_flight = true; s.seq_end = c->pushed;
+    last = &s;
+    c->cur = (c->cur + 1) % (uint32_t)c->slabs.size();
+    i += m;
+  }
+  // the caller may reuse its buffers as soon as we return
+  if (last) CU(c, cudaEventSynchronize(last->copied));
+  return slab_acquire(c, c->cur);
+}
+
+int bh_poll_committed(bh_ctx* c, uint64_t* seq) {
+  if (!c) return BH_ERR_INVALID;
+  DeviceGuard guard(c->device);
+  for (auto& s : c->slabs) {
+    if (!s.in_flight) continue;
+    cudaError_t e = cudaEventQuery(s.done);
+    if (e == cudaSuccess) { s.in_flight = false; if (s.seq_end > c->committed) c->committed = s.seq_end; }
+    else if (e != cudaErrorNotReady) return fail(c, BH_ERR_CUDA, "cudaEventQuery: %s", cudaGetErrorString(e));
+    else cudaGetLastError();
+  }
+  if (seq) *seq = c->committed;
+  return BH_OK;
+}
+
+int bh_sync(bh_ctx* c) {
+  if (!c) return BH_ERR_INVALID;
+  DeviceGuard guard(c->device);
+  CU(c, cudaStreamSynchronize(c->st_compute));
+  for (auto& s : c->slabs)
+    if (s.in_flight) { s.in_flight = false; if (s.seq_end > c->committed) c->committed = s.seq_end; }
+  return BH_OK;
+}
+
+int bh_get_counters(bh_ctx* c, bh_counters* out) {
+  if (!c || !out) return BH_ERR_INVALID;
+  DeviceGuard guard(c->device);
+  CU(c, cudaMemcpyAsync(c->h_small, c->T.counters, 8 * 8, cudaMemcpyDeviceToHost, c->st_compute));
+  CU(c, cudaStreamSynchronize(c->st_compute));
+  memcpy(out, c->h_small, sizeof(bh_counters));
+  return counters_status(*out);
+}
+
+int bh_flush(bh_ctx* c, uint64_t* committed_seq) {
+  if (!c) return BH_ERR_INVALID;
+  DeviceGuard guard(c->device);
+  int rc = submit_current(c);
+  if (rc) return rc;
+  rc = bh_sync(c);
+  if (rc) return rc;
+  c->committed = c->pushed;
+  if (committed_seq) *committed_seq = c->committed;
+  bh_counters k;
+  rc = bh_get_counters(c, &k);
+  if (rc == BH_ERR_TABLE_FULL) return fail(c, rc, "%llu events dropped: a window's key table is full (table_capacity %llu)", (unsigned long long)k.dropped_table_full, (unsigned long long)c->T.cap);
+  if (rc == BH_ERR_WINDOW_RING) return fail(c, rc, "%llu events dropped: more than %u windows open (close windows or raise window_ring)", (unsigned long long)k.dropped_window, c->T.ring);
+  return rc;
+}
+
+static int ensure_export(bh_ctx* c, uint64_t cap, bool hist) {
+  if (cap > c->T.stride) cap = c->T.stride;
+  if (cap == 0) cap = 1;
+  if (cap > c->export_cap) {
+    if (c->d_export) cudaFree(c->d_export);
+    if (c->d_export_hist) cudaFree(c->d_export_hist);
+    c->d_export = nullptr; c->d_export_hist = nullptr; c->export_cap = 0;
+    CU(c, cudaMalloc((void**)&c->d_export, cap * sizeof(bh_record)));
+    c->export_cap = cap;
+  }
+  if (hist && c->T.hist && !c->d_export_hist)
+    CU(c, cudaMalloc((void**)&c->d_export_hist, c->export_cap * c->T.hist_buckets * 4));
+  return BH_OK;
+}
+
+int bh_snapshot_hist(bh_ctx* c, uint64_t window_id, bh_record* out, uint32_t* hist_out, uint64_t cap, uint64_t* n) {
+  if (!c || !n || (cap && !out)) return fail(c, BH_ERR_INVALID, "null argument");
+  DeviceGuard guard(c->device);
+  int rc = submit_current(c);
+  if (rc) return rc;
+  bool hist = hist_out != nullptr && c->T.hist != nullptr;
+  rc = ensure_export(c, cap, hist);
+  if (rc) return rc;
+  uint64_t dcap = std::min<uint64_t>(cap, c->export_cap);
+  CU(c, launch_export(c->S, c->T, window_id, 1, c->d_export, hist ? c->d_export_hist : nullptr, dcap,
+                      c->d_owner_counts, c->d_owner_cursor, c->st_compute));
+  CU(c, cudaMemcpyAsync(c->h_small, c->d_owner_counts, 8, cudaMemcpyDeviceToHost, c->st_compute));
+  CU(c, cudaStreamSynchronize(c->st_compute));
+  uint64_t rows = c->h_small[0];
+  *n = rows;
+  uint64_t take = std::min(rows, dcap);
+  if (take) {
+    CU(c, cudaMemcpy(out, c->d_export, take * sizeof(bh_record), cudaMemcpyDeviceToHost));
+    if (hist) CU(c, cudaMemcpy(hist_out, c->d_export_hist, take * c->T.hist_buckets * 4, cudaMemcpyDeviceToHost));
+  }
+  return BH_OK;
+}
+
+int bh_snapshot(bh_ctx* c, uint64_t window_id, bh_record* out, uint64_t cap, uint64_t* n) {
+  return bh_snapshot_hist(c, window_id, out, nullptr, cap, n);
+}
+
+int bh_list_windows(bh_ctx* c, uint64_t* out, uint32_t cap, uint32_t* n) {
+  if (!c || !n) return BH_ERR_INVALID;
+  DeviceGuard guard(c->device);
+  int rc = submit_current(c);
+  if (rc) return rc;
+  CU(c, cudaMemcpyAsync(c->h_small, c->T.ring_win, (size_t)c->T.ring * 8, cudaMemcpyDeviceToHost, c->st_compute));
+  CU(c, cudaStreamSynchronize(c->st_compute));
+  std::vector<uint64_t> w;
+  for (uint32_t i = 0; i < c->T.ring; i++) if (c->h_small[i] != kNoWindow) w.push_back(c->h_small[i]);
+  std::sort(w.begin(), w.end());
+  *n = (uint32_t)w.size();
+  for (uint32_t i = 0; i < w.size() && i < cap && out; i++) out[i] = w[i];
+  return BH_OK;
+}
+
+int bh_close_window(bh_ctx* c, uint64_t window_id) {
+  if (!c) return BH_ERR_INVALID;
+  DeviceGuard guard(c->device);
+  int rc = submit_current(c);
+  if (rc) return rc;
+  CU(c, launch_close_window(c->T, window_id, c->st_compute));
+  return BH_OK;
+}
+
+// ---- device-resident entry points ----
+int bh_process_device(bh_ctx* c, const uint8_t* d_payload, const uint32_t* d_offsets, const uint64_t* d_ts,
+                      uint32_t n, void* stream) {
+  if (!c || (n && (!d_payload || !d_offsets))) return fail(c, BH_ERR_INVALID, "null argument");
+  if (((uintptr_t)d_payload & 15) != 0) return fail(c, BH_ERR_INVALID, "d_payload must be 16-byte aligned");
+  if (c->S.has_window && !d_ts && n) return fail(c, BH_ERR_INVALID, "d_ts_ms required in windowed mode");
+  DeviceGuard guard(c->device);
+  cudaStream_t st = stream ? (cudaStream_t)stream : c->st_compute;
+  CU(c, launch_process_raw(c->S, c->T, c->G, d_payload, d_offsets, d_ts, n, st, &c->launches));
+  return BH_OK;
+}
+
+int bh_process_columns_device(bh_ctx* c, const uint64_t* d_kh, const uint64_t* d_ts, const double* d_val,
+                              uint64_t n, void* stream) {
+  if (!c || (n && !d_kh)) return fail(c, BH_ERR_INVALID, "null argument");
+  if (c->S.mode != BH_MODE_WINDOWED) return fail(c, BH_ERR_INVALID, "needs BH_MODE_WINDOWED");
+  if (c->S.has_window && !d_ts && n) return fail(c, BH_ERR_INVALID, "d_ts_ms required in windowed mode");
+  DeviceGuard guard(c->device);
+  cudaStream_t st = stream ? (cudaStream_t)stream : c->st_compute;
+  CU(c, launch_process_columns(c->S, c->T, c->G, d_kh, d_ts, d_val, n, st, &c->launches));
+  return BH_OK;
+}
+
+int bh_decode_device(bh_ctx* c, const uint8_t* d_payload, const uint32_t* d_offsets, uint32_t n,
+                     uint64_t* d_kh, double* d_val, int32_t* d_status, uint8_t* d_outcome, void* stream) {
+  if (!c || (n && (!d_payload || !d_offsets || !d_kh || !d_val || !d_status || !d_outcome))) return fail(c, BH_ERR_INVALID, "null argument");
+  if (((uintptr_t)d_payload & 15) != 0) return fail(c, BH_ERR_INVALID, "d_payload must be 16-byte aligned");
+  DeviceGuard guard(c->device);
+  cudaStream_t st = stream ? (cudaStream_t)stream : c->st_compute;
+  CU(c, launch_decode(c->S, c->G, d_payload, d_offsets, n, d_kh, d_val, d_status, d_outcome, st));
+  return BH_OK;
+}
+
+int bh_export_window_device(bh_ctx* c, uint64_t window_id, uint32_t n_owners, bh_record* d_records,
+                            uint32_t* d_hist, uint64_t cap, uint64_t* d_owner_counts, void* stream) {
+  if (!c || !d_records || !d_owner_counts) return fail(c, BH_ERR_INVALID, "null argument");
+  if (!is_pow2(n_owners) || n_owners > 1024) return fail(c, BH_ERR_INVALID, "n_owners must be a power of two <= 1024");
+  DeviceGuard guard(c->device);
+  cudaStream_t st = stream ? (cudaStream_t)stream : c->st_compute;
+  CU(c, launch_export(c->S, c->T, window_id, n_owners, d_records, d_hist, cap,
+                      (unsigned long long*)d_owner_counts, c->d_owner_cursor, st));
+  return BH_OK;
+}
+
+int bh_merge_records_device(bh_ctx* c, const bh_record* d_records, const uint32_t* d_hist, uint64_t n, void* stream) {
+  if (!c || (n && !d_records)) return fail(c, BH_ERR_INVALID, "null argument");
+  DeviceGuard guard(c->device);
+  cudaStream_t st = stream ? (cudaStream_t)stream : c->st_compute;
+  CU(c, launch_merge(c->S, c->T, d_records, d_hist, n, st));
+  return BH_OK;
+}
+
+// test hook: floor(n / d) through the same routine the kernels use for window ids
+uint64_t bh_debug_div64(uint64_t n, uint64_t d) { return d ? div64(n, make_div64(d)) : 0; }
+
+}  // extern "C"

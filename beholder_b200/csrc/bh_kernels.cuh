@@ -1,0 +1,35 @@
+// bh_kernels.cuh — host-side launchers of the sm_100a kernels (defined in bh_kernels.cu).
+#pragma once
+#include "bh_common.cuh"
+
+namespace bh {
+
+struct LaunchGeom {
+  int sms;            // SM count of the device
+  int smem_optin;     // max opt-in dynamic shared memory per block
+};
+
+// fused proto.decode + enum check + aggregate over one raw batch (index.js:129-138)
+cudaError_t launch_process_raw(const DevSchema& S, const DevTables& T, const LaunchGeom& G,
+                               const uint8_t* payload, const uint32_t* offsets, const uint64_t* ts,
+                               uint32_t n, cudaStream_t st, int* launches);
+// aggregate pre-decoded columns
+cudaError_t launch_process_columns(const DevSchema& S, const DevTables& T, const LaunchGeom& G,
+                                   const uint64_t* kh, const uint64_t* ts, const double* val,
+                                   uint64_t n, cudaStream_t st, int* launches);
+// decode only -> columns
+cudaError_t launch_decode(const DevSchema& S, const LaunchGeom& G, const uint8_t* payload,
+                          const uint32_t* offsets, uint32_t n, uint64_t* kh, double* val,
+                          int32_t* status, uint8_t* outcome, cudaStream_t st);
+// compact one window into records grouped by owner (two passes: count, scatter)
+cudaError_t launch_export(const DevSchema& S, const DevTables& T, uint64_t window_id, uint32_t n_owners,
+                          bh_record* out, uint32_t* hist_out, uint64_t cap,
+                          unsigned long long* owner_counts, unsigned long long* owner_cursor,
+                          cudaStream_t st);
+cudaError_t launch_merge(const DevSchema& S, const DevTables& T, const bh_record* recs,
+                         const uint32_t* hist, uint64_t n, cudaStream_t st);
+cudaError_t launch_close_window(const DevTables& T, uint64_t window_id, cudaStream_t st);
+cudaError_t configure_kernels(const LaunchGeom& G);
+cudaError_t launch_init_tables(const DevTables& T, cudaStream_t st);
+
+}  // namespace bh

@@ -1,0 +1,225 @@
+"""Aggregator: thin object wrapper over the C-ABI context (bh_ctx).
+
+All compute happens in libbeholder_gpu.so on the GPU.  numpy is used only to hold host
+buffers; torch (optional) only to hold device buffers handed to the *_device entry points.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional, Sequence
+
+import numpy as np
+
+from . import _lib as L
+from .schema import Schema, fill_config, telemetry_progress
+
+RECORD_DTYPE = np.dtype([("key_hash", "<u8"), ("window_id", "<u8"), ("count", "<u8"),
+                         ("sum", "<f8"), ("min", "<f8"), ("max", "<f8")])
+assert RECORD_DTYPE.itemsize == C.sizeof(L.BhRecord)
+
+DEFAULT_HIST_E0 = 991   # bucket 32 <-> [1, 2)
+
+
+def _ptr(a) -> Optional[int]:
+    """address of a numpy array / torch tensor / int / None"""
+    if a is None:
+        return None
+    if isinstance(a, int):
+        return a
+    if isinstance(a, np.ndarray):
+        return a.ctypes.data
+    if hasattr(a, "data_ptr"):
+        return a.data_ptr()
+    raise TypeError(type(a))
+
+
+class Aggregator:
+    """One GPU's group-by state: replaces the prom-client Counter of index.js:30-34 (REFERENCE
+    mode) or holds the windowed count/sum/min/max/histogram tables (WINDOWED mode)."""
+
+    def __init__(self, schema: Optional[Schema] = None, *, mode: int = L.MODE_WINDOWED,
+                 key: Sequence[str] = ("mediaId", "status"), ops: int = L.OP_COUNT | L.OP_SUM | L.OP_MIN | L.OP_MAX,
+                 window_ms: int = 10_000, window_ring: int = 0, table_capacity: int = 0,
+                 hist_buckets: int = 64, hist_e0: int = DEFAULT_HIST_E0, hash_seed: int = 0xBE401DE5,
+                 device: int = 0, slab_bytes: int = 0, slab_events: int = 0, n_slabs: int = 0,
+                 enum_drop: bool = True):
+        schema = schema or telemetry_progress()
+        if mode == L.MODE_WINDOWED:
+            schema = schema.with_roles(key=key)
+        self.schema = schema
+        cfg = L.BhConfig()
+        cfg.struct_size = C.sizeof(cfg)
+        cfg.device = device
+        cfg.mode = mode
+        cfg.ops = ops
+        cfg.window_ms = window_ms if mode == L.MODE_WINDOWED else 0
+        cfg.window_ring = window_ring
+        cfg.hist_buckets = hist_buckets
+        cfg.hist_e0 = hist_e0
+        cfg.table_capacity = table_capacity
+        cfg.hash_seed = hash_seed
+        cfg.slab_bytes = slab_bytes
+        cfg.slab_events = slab_events
+        cfg.n_slabs = n_slabs
+        fill_config(cfg, schema)
+        if not enum_drop:
+            cfg.n_enum = 0
+        self.cfg = cfg
+        self.mode = mode
+        self.ops = ops | L.OP_COUNT if mode == L.MODE_WINDOWED else L.OP_COUNT
+        self.hist_buckets = hist_buckets or 64
+        self.device = device
+        self._ctx = C.c_void_p()
+        L.check(L.lib.bh_create(C.byref(cfg), C.byref(self._ctx)))
+
+    # ---- lifecycle ----
+    def close(self) -> None:
+        if self._ctx:
+            L.lib.bh_destroy(self._ctx)
+            self._ctx = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def _ck(self, rc: int) -> int:
+        return L.check(rc, self._ctx)
+
+    # ---- ingest ----
+    def push(self, payload: bytes, ts_ms: int = 0) -> None:
+        buf = (C.c_char * len(payload)).from_buffer_copy(payload) if payload else None
+        self._ck(L.lib.bh_push(self._ctx, C.addressof(buf) if buf is not None else None, len(payload), ts_ms))
+
+    def push_batch(self, slab, offsets, ts_ms=None, *, pinned: bool = False) -> None:
+        n = len(offsets) - 1
+        fn = L.lib.bh_push_batch_pinned if pinned else L.lib.bh_push_batch
+        self._ck(fn(self._ctx, _ptr(slab), _ptr(offsets), _ptr(ts_ms), n))
+
+    def push_columns(self, key_hash, ts_ms, value) -> None:
+        self._ck(L.lib.bh_push_columns(self._ctx, _ptr(key_hash), _ptr(ts_ms), _ptr(value), len(key_hash)))
+
+    def flush(self) -> int:
+        seq = C.c_uint64()
+        self._ck(L.lib.bh_flush(self._ctx, C.byref(seq)))
+        return seq.value
+
+    def poll_committed(self) -> int:
+        seq = C.c_uint64()
+        self._ck(L.lib.bh_poll_committed(self._ctx, C.byref(seq)))
+        return seq.value
+
+    def sync(self) -> None:
+        self._ck(L.lib.bh_sync(self._ctx))
+
+    # ---- device-resident entry points (pointers or torch tensors) ----
+    def process_device(self, d_payload, d_offsets, d_ts, n: int, stream: int = 0) -> None:
+        self._ck(L.lib.bh_process_device(self._ctx, _ptr(d_payload), _ptr(d_offsets), _ptr(d_ts), n, stream or None))
+
+    def process_columns_device(self, d_kh, d_ts, d_val, n: int, stream: int = 0) -> None:
+        self._ck(L.lib.bh_process_columns_device(self._ctx, _ptr(d_kh), _ptr(d_ts), _ptr(d_val), n, stream or None))
+
+    def decode_device(self, d_payload, d_offsets, n: int, d_kh, d_val, d_status, d_outcome, stream: int = 0) -> None:
+        self._ck(L.lib.bh_decode_device(self._ctx, _ptr(d_payload), _ptr(d_offsets), n, _ptr(d_kh), _ptr(d_val),
+                                        _ptr(d_status), _ptr(d_outcome), stream or None))
+
+    def export_window_device(self, window_id: int, n_owners: int, d_records, d_hist, cap: int, d_owner_counts,
+                             stream: int = 0) -> None:
+        self._ck(L.lib.bh_export_window_device(self._ctx, window_id, n_owners, _ptr(d_records), _ptr(d_hist), cap,
+                                               _ptr(d_owner_counts), stream or None))
+
+    def merge_records_device(self, d_records, d_hist, n: int, stream: int = 0) -> None:
+        self._ck(L.lib.bh_merge_records_device(self._ctx, _ptr(d_records), _ptr(d_hist), n, stream or None))
+
+    # ---- read side ----
+    def snapshot(self, window_id: int = 0, with_hist: bool = False, cap: int = 0):
+        """rows of one window, sorted by key_hash; (records, hist) when with_hist"""
+        cap = cap or 1 << 16
+        while True:
+            out = np.zeros(cap, dtype=RECORD_DTYPE)
+            hist = np.zeros((cap, self.hist_buckets), dtype=np.uint32) if with_hist else None
+            n = C.c_uint64()
+            self._ck(L.lib.bh_snapshot_hist(self._ctx, window_id, out.ctypes.data,
+                                            hist.ctypes.data if hist is not None else None, cap, C.byref(n)))
+            if n.value <= cap:
+                break
+            cap = int(n.value)
+        out = out[: n.value]
+        order = np.argsort(out["key_hash"], kind="stable")
+        out = out[order]
+        if with_hist:
+            return out, hist[: n.value][order]
+        return out
+
+    def snapshot_all(self, with_hist: bool = False):
+        recs, hists = [], []
+        for w in self.list_windows():
+            r = self.snapshot(w, with_hist)
+            if with_hist:
+                recs.append(r[0]); hists.append(r[1])
+            else:
+                recs.append(r)
+        if not recs:
+            empty = np.zeros(0, dtype=RECORD_DTYPE)
+            return (empty, np.zeros((0, self.hist_buckets), np.uint32)) if with_hist else empty
+        return (np.concatenate(recs), np.concatenate(hists)) if with_hist else np.concatenate(recs)
+
+    def list_windows(self):
+        out = np.zeros(1024, dtype=np.uint64)
+        n = C.c_uint32()
+        self._ck(L.lib.bh_list_windows(self._ctx, out.ctypes.data, 1024, C.byref(n)))
+        return [int(x) for x in out[: n.value]]
+
+    def close_window(self, window_id: int) -> None:
+        self._ck(L.lib.bh_close_window(self._ctx, window_id))
+
+    def counters(self, check: bool = True) -> dict:
+        k = L.BhCounters()
+        rc = L.lib.bh_get_counters(self._ctx, C.byref(k))
+        if check and rc not in (L.BH_OK,):
+            self._ck(rc)
+        return {f: getattr(k, f) for f, _ in L.BhCounters._fields_ if f != "reserved"}
+
+    # ---- REFERENCE mode convenience: the Counter's label -> value map ----
+    def status_counts(self) -> dict:
+        """{lower-cased enum name: count} == beholder_progress_updates_total{status=...} (index.js:136-138)"""
+        recs = self.snapshot(0)
+        out = {}
+        for r in recs:
+            name = self.schema.enum_name(int(r["key_hash"]))
+            if name is not None:
+                out[name.lower()] = int(r["count"])
+        return out
+
+
+class PinnedBuffer:
+    """page-locked host memory from bh_host_alloc, viewed as a numpy array"""
+
+    def __init__(self, nbytes: int):
+        p = C.c_void_p()
+        L.check(L.lib.bh_host_alloc(C.byref(p), max(nbytes, 1)))
+        self.ptr = p.value
+        self.nbytes = nbytes
+        self._buf = (C.c_uint8 * max(nbytes, 1)).from_address(self.ptr)
+
+    def view(self, dtype, count: Optional[int] = None, offset: int = 0) -> np.ndarray:
+        return np.frombuffer(self._buf, dtype=dtype, count=-1 if count is None else count, offset=offset)
+
+    def free(self) -> None:
+        if self.ptr:
+            self._buf = None
+            L.lib.bh_host_free(self.ptr)
+            self.ptr = None
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass

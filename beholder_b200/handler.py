@@ -1,0 +1,212 @@
+"""Host-side mirror of the reference's handler interface for the progress path.
+
+The reference (JavaScript, index.js) wires the path like this:
+
+    const prom = Prom.new('beholder'); Prom.expose()                            // index.js:27-28
+    metrics.progress_updates_total = new prom.Counter({name, help, labelNames}) // index.js:30-34
+    amqp.listen('v1.telemetry.progress', async rmsg => { ...; rmsg.ack() })     // index.js:127-155
+
+Node is not available in this image, so the host side above the C-ABI is written in Python
+with the same names, argument meaning and error behaviour; addon/ holds the N-API shim and the
+JS wrapper a maintainer would ship.  The drop-in is:
+
+    gpu = BeholderGPU()                                     # replaces the Counter + decode + inc
+    amqp.listen('v1.telemetry.progress', gpu.handler(side_effects))
+    gpu.progress_updates_total.get()                        # what the /metrics scrape reads
+
+`handler` returns an `async rmsg => ...` callable: it copies `rmsg.message.content` into the
+pinned ingest ring (bh_push), keeps `rmsg` and acks it exactly once when the batch holding it
+has been aggregated on the GPU (index.js:151,154: every message is acked, dropped or not).
+"""
+from __future__ import annotations
+
+import asyncio
+import collections
+import inspect
+from typing import Awaitable, Callable, Deque, Dict, List, Optional, Tuple
+
+from . import _lib as L
+from .engine import Aggregator
+from .schema import Schema, telemetry_progress
+
+COUNTER_NAME = "beholder_progress_updates_total"                                       # index.js:31
+COUNTER_HELP = "Total number of messages processed in this processes lifetime"         # index.js:32
+
+
+class GpuCounter:
+    """prom-client Counter look-alike whose values live in the GPU table (index.js:30-34)."""
+
+    def __init__(self, owner: "BeholderGPU", name: str = COUNTER_NAME, help: str = COUNTER_HELP,
+                 label_names=("status",)):
+        self._owner = owner
+        self.name = name
+        self.help = help
+        self.labelNames = list(label_names)
+
+    def get(self) -> dict:
+        """same shape as prom-client 11.x Counter.get()"""
+        counts = self._owner.status_counts()
+        return {
+            "help": self.help, "name": self.name, "type": "counter", "aggregator": "sum",
+            "values": [{"value": v, "labels": {"status": k}} for k, v in counts.items()],
+        }
+
+    def inc(self, labels=None, value=1):
+        raise TypeError("beholder_progress_updates_total is incremented on the GPU by the progress handler; "
+                        "there is no host-side inc()")
+
+    def metrics(self) -> str:
+        """prom-client registry.metrics() text for this counter"""
+        lines = [f"# HELP {self.name} {self.help}", f"# TYPE {self.name} counter"]
+        for k, v in self._owner.status_counts().items():
+            lines.append(f'{self.name}{{status="{k}"}} {v}')
+        return "\n".join(lines) + "\n"
+
+
+class HostCounter:
+    """plain host counter for the side-effect metrics (beholder_trello_comments, index.js:35-39)"""
+
+    def __init__(self, name: str, help: str = ""):
+        self.name, self.help, self.value = name, help, 0
+
+    def inc(self, value: int = 1):
+        self.value += value
+
+    def metrics(self) -> str:
+        return f"# HELP {self.name} {self.help}\n# TYPE {self.name} counter\n{self.name} {self.value}\n"
+
+
+class BeholderGPU:
+    """`require('beholder-gpu')(cfg)` of SURVEY §8b."""
+
+    def __init__(self, schema: Optional[Schema] = None, device: int = 0, commit_every: int = 65536,
+                 slab_bytes: int = 0, slab_events: int = 0, logger=None):
+        self.schema = schema or telemetry_progress()
+        self.agg = Aggregator(self.schema, mode=L.MODE_REFERENCE, device=device,
+                              slab_bytes=slab_bytes, slab_events=slab_events)
+        self.commit_every = commit_every
+        self.logger = logger
+        self._pending: Deque[Tuple[int, object]] = collections.deque()   # (sequence number, rmsg)
+        self._seq = 0
+        self.progress_updates_total = GpuCounter(self)
+        self.trello_comments_total = HostCounter("beholder_trello_comments",
+                                                 "Total trello comments crreated in this processes lifetime")
+
+    # -- the handler: amqp.listen('v1.telemetry.progress', gpu.handler(fn)) --
+    def handler(self, side_effects: Optional[Callable[[object], Optional[Awaitable]]] = None):
+        async def on_progress(rmsg):
+            content = rmsg.message.content
+            self.agg.push(bytes(content))
+            self._seq += 1
+            self._pending.append((self._seq, rmsg))
+            if side_effects is not None:
+                # index.js:140-148 stay on the host, per event; their failure neither un-counts the
+                # event nor stops the ack (index.js:149-152)
+                try:
+                    r = side_effects(rmsg)
+                    if inspect.isawaitable(r):
+                        await r
+                except Exception as err:  # noqa: BLE001 - mirrors `catch (err)` at index.js:149
+                    if self.logger:
+                        self.logger.warning("failed to update media progress %s", err)
+            if len(self._pending) >= self.commit_every:
+                self.commit()
+            else:
+                self._ack_upto(self.agg.poll_committed())
+        return on_progress
+
+    def _ack_upto(self, seq: int) -> int:
+        n = 0
+        while self._pending and self._pending[0][0] <= seq:
+            _, rmsg = self._pending.popleft()
+            rmsg.ack()
+            n += 1
+        return n
+
+    def commit(self) -> int:
+        """aggregate everything received so far, then ack it; returns the number of acks sent"""
+        return self._ack_upto(self.agg.flush())
+
+    def status_counts(self) -> Dict[str, int]:
+        self.commit()
+        return self.agg.status_counts()
+
+    def dropped(self) -> Dict[str, int]:
+        k = self.agg.counters()
+        return {"decode": k["dropped_decode"], "enum": k["dropped_enum"]}
+
+    def metrics(self) -> str:
+        """the body Prom.expose() serves for these two counters (index.js:28)"""
+        return self.progress_updates_total.metrics() + self.trello_comments_total.metrics()
+
+    def close(self):
+        self.commit()
+        self.agg.close()
+
+
+# --------------------------------------------------------------------------------------------
+# local stub queue: stands in for triton-core/amqp in tests and BASELINE.json config 1
+# --------------------------------------------------------------------------------------------
+class _Message:
+    __slots__ = ("content",)
+
+    def __init__(self, content: bytes):
+        self.content = content
+
+
+class StubRmsg:
+    """the `rmsg` triton-core/amqp hands to a listener: .message.content and .ack()"""
+    __slots__ = ("message", "acks", "_queue")
+
+    def __init__(self, content: bytes, queue: "StubAMQP"):
+        self.message = _Message(content)
+        self.acks = 0
+        self._queue = queue
+
+    def ack(self):
+        self.acks += 1
+        self._queue.acked += 1
+
+
+class StubAMQP:
+    """in-memory `new AMQP(addr, prefetch, ...)` with listen()/publish() (index.js:43,62,127)"""
+
+    def __init__(self, prefetch: int = 100):
+        self.prefetch = prefetch
+        self.listeners: Dict[str, Callable] = {}
+        self.queues: Dict[str, List[bytes]] = collections.defaultdict(list)
+        self.delivered: List[StubRmsg] = []
+        self.acked = 0
+
+    async def connect(self):
+        return None
+
+    def listen(self, topic: str, fn: Callable):
+        self.listeners[topic] = fn
+
+    def publish(self, topic: str, content: bytes):
+        self.queues[topic].append(content)
+
+    async def run(self):
+        """deliver everything queued, at most `prefetch` handler invocations in flight"""
+        sem = asyncio.Semaphore(self.prefetch)
+
+        async def deliver(fn, rmsg):
+            try:
+                await fn(rmsg)
+            finally:
+                sem.release()
+
+        tasks = []
+        for topic, msgs in self.queues.items():
+            fn = self.listeners.get(topic)
+            if fn is None:
+                continue
+            for content in msgs:
+                await sem.acquire()
+                rmsg = StubRmsg(content, self)
+                self.delivered.append(rmsg)
+                tasks.append(asyncio.ensure_future(deliver(fn, rmsg)))
+            msgs.clear()
+        if tasks:
+            await asyncio.gather(*tasks)

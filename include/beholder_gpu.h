@@ -1,0 +1,201 @@
+/*
+ * beholder_gpu.h — C-ABI of libbeholder_gpu.so: the B200 (sm_100a) implementation of
+ * beholder's progress-event consume-and-aggregate path.
+ *
+ * This is the drop-in boundary: the N-API addon (addon/beholder_napi.c), the Python
+ * host mirror (beholder_b200/) and the tests all bind exactly these symbols.  Plain
+ * pointers and sizes only; no exceptions cross it; every function returns a bh_status
+ * (0 = OK, negative = error, text via bh_last_error).  There is no CPU fallback: with no
+ * sm_100 device bh_create fails with BH_ERR_NO_DEVICE.
+ *
+ * Citations "index.js:N" are into the reference, /root/reference/index.js.
+ */
+#ifndef BEHOLDER_GPU_H
+#define BEHOLDER_GPU_H
+#include <stdint.h>
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum {
+  BH_OK = 0,
+  BH_ERR_INVALID = -1,       /* bad argument / config */
+  BH_ERR_NO_DEVICE = -2,     /* no CUDA device of compute capability 10.x */
+  BH_ERR_CUDA = -3,          /* a CUDA call failed; see bh_last_error */
+  BH_ERR_NOMEM = -4,
+  BH_ERR_TABLE_FULL = -5,    /* a window's key table overflowed: events were dropped */
+  BH_ERR_WINDOW_RING = -6,   /* more simultaneously open windows than window_ring */
+  BH_ERR_TOO_LARGE = -7,     /* batch exceeds a u32 offset / slab limit */
+  BH_ERR_UNSUPPORTED = -8    /* schema uses a field number or type the kernels do not take */
+} bh_status;
+
+/* declared scalar type of a known field = the protobufjs reader call the generated
+ * decoder makes for it (proto.decode, index.js:129) */
+enum {
+  BH_K_STRING = 1, BH_K_BYTES = 2, BH_K_INT32 = 3 /* int32, enum */, BH_K_UINT32 = 4,
+  BH_K_SINT32 = 5, BH_K_BOOL = 6, BH_K_FLOAT = 7, BH_K_DOUBLE = 8
+};
+/* role bits of a field on this path */
+enum {
+  BH_R_KEY = 1,      /* part of the grouping key (windowed mode), schema order */
+  BH_R_STATUS = 2,   /* `status`: the enum whose name is the reference's only label (index.js:134-138) */
+  BH_R_VALUE = 4     /* `progress`: the reduced value (extension; index.js:143 only prints it) */
+};
+enum { BH_OP_COUNT = 1, BH_OP_SUM = 2, BH_OP_MIN = 4, BH_OP_MAX = 8, BH_OP_HIST = 16 };
+enum {
+  BH_MODE_REFERENCE = 0,  /* index.js:127-138 exactly: key = status, cumulative count, no window */
+  BH_MODE_WINDOWED = 1    /* extension: key fields x tumbling window, ops */
+};
+/* per-event outcome written by bh_decode_device */
+enum { BH_EV_OK = 0, BH_EV_DROP_DECODE = 1, BH_EV_DROP_ENUM = 2, BH_EV_DROP_NAN = 3 };
+
+#define BH_MAX_FIELDS 16
+#define BH_MAX_ENUM 64
+#define BH_MAX_KEY_PARTS 3
+#define BH_MAX_FIELD_NUMBER 31
+#define BH_HIST_MAX 64
+
+typedef struct { uint32_t number, kind, role, reserved; } bh_field;
+
+/* Replaces the construction at index.js:27-48 (Prom.new, new AMQP, proto.load): everything the
+ * device path needs to know about api.TelemetryProgress.  The .proto ships in triton-core, not in
+ * the reference tree, so field numbers and the enum list are supplied by the caller. */
+typedef struct bh_config {
+  uint32_t struct_size;        /* sizeof(bh_config), checked */
+  int32_t device;              /* CUDA ordinal */
+  uint32_t mode;               /* BH_MODE_* */
+  uint32_t ops;                /* BH_OP_* (REFERENCE mode forces COUNT) */
+  uint64_t window_ms;          /* tumbling window; 0 = one cumulative window, id 0 */
+  uint32_t window_ring;        /* simultaneously open windows, power of two, <= 1024 */
+  uint32_t hist_buckets;       /* <= 64; 0 -> 64 */
+  int32_t hist_e0;             /* bucket = clamp(biased_exponent(v) - e0, 1, B-1); 0 for v <= 0 */
+  uint32_t n_fields;
+  bh_field fields[BH_MAX_FIELDS];
+  uint32_t n_enum;             /* valid numbers of TelemetryStatusEntry (each 0..63); 0 = no enum drop rule */
+  int32_t enum_numbers[BH_MAX_ENUM];
+  uint64_t table_capacity;     /* key slots per window, power of two */
+  uint64_t hash_seed;
+  uint64_t slab_bytes;         /* ingest ring: payload bytes per slab (0 -> 64 MiB) */
+  uint32_t slab_events;        /* ingest ring: events per slab (0 -> 1 Mi) */
+  uint32_t n_slabs;            /* ingest ring depth (0 -> 3) */
+} bh_config;
+
+/* One aggregate row.  REFERENCE mode: key_hash = status number, window_id = 0, count = the value of
+ * beholder_progress_updates_total{status=<name>} (index.js:30-34). */
+typedef struct bh_record {
+  uint64_t key_hash, window_id, count;
+  double sum, min, max;
+} bh_record;
+
+typedef struct bh_counters {
+  uint64_t events_ok;          /* aggregated */
+  uint64_t dropped_decode;     /* proto.decode threw -> warn + ack, not counted (index.js:149-152) */
+  uint64_t dropped_enum;       /* enumToString undefined -> TypeError -> same catch (index.js:134,137) */
+  uint64_t dropped_nan;        /* extension */
+  uint64_t dropped_table_full; /* -> BH_ERR_TABLE_FULL */
+  uint64_t dropped_window;     /* -> BH_ERR_WINDOW_RING */
+  uint64_t smem_spills;        /* events that bypassed the shared-memory table (diagnostic) */
+  uint64_t reserved;
+} bh_counters;
+
+typedef struct bh_ctx bh_ctx;
+
+/* ---- lifecycle: replaces index.js:27-48 ---- */
+int bh_create(const bh_config* cfg, bh_ctx** out);
+void bh_destroy(bh_ctx* ctx);
+const char* bh_last_error(bh_ctx* ctx);   /* ctx may be NULL: last bh_create error of this thread */
+int bh_device_count(void);                /* CUDA devices of compute capability 10.x */
+
+/* ---- ingest: replaces the body of `amqp.listen('v1.telemetry.progress', async rmsg => ...)`,
+ * index.js:127-138.  The caller keeps rmsg and acks it once bh_poll_committed passes its sequence
+ * number (index.js:151,154: every message is acked exactly once, dropped or not). ---- */
+/* one message: rmsg.message.content (index.js:129).  Copied into the pinned ring before returning. */
+int bh_push(bh_ctx* ctx, const uint8_t* payload, uint32_t len, uint64_t ts_ms);
+/* n messages: slab + n+1 byte offsets (offsets[0] may be non-zero) + n timestamps (may be NULL = 0) */
+int bh_push_batch(bh_ctx* ctx, const uint8_t* slab, const uint32_t* offsets, const uint64_t* ts_ms, uint32_t n);
+/* same, but slab/offsets/ts_ms are in pinned host memory (bh_host_alloc) and stay valid until
+ * committed: copied to the device straight from the caller's buffers. */
+int bh_push_batch_pinned(bh_ctx* ctx, const uint8_t* slab, const uint32_t* offsets, const uint64_t* ts_ms, uint32_t n);
+/* pre-decoded columns (the counter side alone: metrics.progress_updates_total.inc, index.js:136-138) */
+int bh_push_columns(bh_ctx* ctx, const uint64_t* key_hash, const uint64_t* ts_ms, const double* value, uint64_t n);
+/* submit the partial slab and wait until everything pushed so far is aggregated */
+int bh_flush(bh_ctx* ctx, uint64_t* committed_seq);
+/* non-blocking: number of events whose aggregation has completed on the device */
+int bh_poll_committed(bh_ctx* ctx, uint64_t* seq);
+int bh_host_alloc(void** out, size_t bytes);   /* pinned host memory for bh_push_batch_pinned */
+int bh_host_free(void* p);
+
+/* ---- read side: what Prom.expose() serves (index.js:28) ---- */
+/* rows of one window (REFERENCE mode: window 0) in unspecified order; *n = rows available */
+int bh_snapshot(bh_ctx* ctx, uint64_t window_id, bh_record* out, uint64_t cap, uint64_t* n);
+/* same plus per-row log2 histograms, hist_out[cap * hist_buckets] */
+int bh_snapshot_hist(bh_ctx* ctx, uint64_t window_id, bh_record* out, uint32_t* hist_out, uint64_t cap, uint64_t* n);
+int bh_list_windows(bh_ctx* ctx, uint64_t* out, uint32_t cap, uint32_t* n);
+/* drop a window's table so its ring slot can be reused */
+int bh_close_window(bh_ctx* ctx, uint64_t window_id);
+/* drops / diagnostics; returns BH_ERR_TABLE_FULL / BH_ERR_WINDOW_RING if events were lost that way */
+int bh_get_counters(bh_ctx* ctx, bh_counters* out);
+
+/* ---- device-resident entry points (inputs/outputs already in HBM; asynchronous on `stream`,
+ * a cudaStream_t passed as void*, NULL = the context's own stream).  Used by bench.py's
+ * kernel-only measurement and by the multi-GPU exchange. ---- */
+/* fused proto.decode + enumToString + counter update (index.js:129-138) over one batch.
+ * d_payload must be 16-byte aligned and readable up to offsets[n] rounded up to 16. */
+int bh_process_device(bh_ctx* ctx, const uint8_t* d_payload, const uint32_t* d_offsets,
+                      const uint64_t* d_ts_ms, uint32_t n, void* stream);
+int bh_process_columns_device(bh_ctx* ctx, const uint64_t* d_key_hash, const uint64_t* d_ts_ms,
+                              const double* d_value, uint64_t n, void* stream);
+/* proto.decode alone (index.js:129): payloads -> key-hash / value / status / outcome columns */
+int bh_decode_device(bh_ctx* ctx, const uint8_t* d_payload, const uint32_t* d_offsets, uint32_t n,
+                     uint64_t* d_key_hash, double* d_value, int32_t* d_status, uint8_t* d_outcome,
+                     void* stream);
+/* compact one window into d_records grouped by owner = key_hash >> (64 - log2(n_owners)):
+ * d_owner_counts[n_owners] receives rows per owner, rows of owner o start at sum(counts[<o]).
+ * d_hist may be NULL.  No reference counterpart (the reference is one process). */
+int bh_export_window_device(bh_ctx* ctx, uint64_t window_id, uint32_t n_owners, bh_record* d_records,
+                            uint32_t* d_hist, uint64_t cap, uint64_t* d_owner_counts, void* stream);
+/* merge partial rows (from other GPUs) into this context's tables */
+int bh_merge_records_device(bh_ctx* ctx, const bh_record* d_records, const uint32_t* d_hist,
+                            uint64_t n, void* stream);
+int bh_sync(bh_ctx* ctx);
+
+/* ---- synthetic event streams (bench/test input) ---- */
+typedef struct bh_synth_config {
+  uint32_t struct_size;
+  uint32_t n_status;           /* events use status numbers 0..n_status-1 */
+  uint64_t seed;
+  uint64_t n_keys;             /* distinct (mediaId, status) keys */
+  uint64_t t0_ms;              /* first timestamp */
+  uint32_t rate_per_ms;        /* events per millisecond of stream time */
+  uint32_t jitter_ms;          /* ts = t0 + g / rate + U[-jitter, +jitter] */
+  uint32_t payload_bytes;      /* pad every event to exactly this size when it fits; 0 = natural */
+  uint32_t value_f64;          /* 0: progress = int32 varint 0..100; 1: double, random mantissa/exponent */
+  int32_t value_exp_lo;        /* value_f64: exponent drawn from [lo, lo + span) */
+  uint32_t value_exp_span;
+  uint32_t value_signed;       /* value_f64: random sign */
+  uint32_t malformed_ppm;      /* corrupted events per million */
+  uint32_t unknown_enum_ppm;   /* events whose status has no enum name, per million */
+  uint32_t zipf;               /* 0 uniform; 1: keys drawn through d_zipf_cdf */
+} bh_synth_config;
+/* bytes event g occupies (host helper, same function the device uses) */
+uint32_t bh_synth_event_size(const bh_synth_config* c, uint64_t g, const uint64_t* zipf_cdf);
+/* write event g into out (>= bh_synth_event_size bytes); returns its size and timestamp */
+uint32_t bh_synth_event_host(const bh_synth_config* c, uint64_t g, const uint64_t* zipf_cdf,
+                             uint8_t* out, uint64_t* ts_ms);
+/* generate events [first, first+n) on the device: d_offsets[n+1], d_ts[n], payload written at
+ * d_payload (capacity checked against the total, returned in *total_bytes). d_zipf_cdf[n_keys]
+ * (u64 thresholds) is required when zipf != 0. */
+int bh_synth_generate_device(int device, const bh_synth_config* c, uint64_t first, uint32_t n,
+                             const uint64_t* d_zipf_cdf, uint8_t* d_payload, uint64_t payload_cap,
+                             uint32_t* d_offsets, uint64_t* d_ts, uint64_t* total_bytes, void* stream);
+/* columns of the same stream without the wire format: key hash as the fused path would compute it */
+int bh_synth_columns_device(int device, const bh_synth_config* c, uint64_t hash_seed, uint64_t first,
+                            uint64_t n, const uint64_t* d_zipf_cdf, uint64_t* d_key_hash,
+                            uint64_t* d_ts, double* d_value, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
