@@ -509,7 +509,7 @@ int bh_snapshot_hist(bh_ctx* c, uint64_t window_id, bh_record* out, uint32_t* hi
   rc = ensure_export(c, cap, hist);
   if (rc) return rc;
   uint64_t dcap = std::min<uint64_t>(cap, c->export_cap);
-  CU(c, launch_export(c->S, c->T, window_id, 1, c->d_export, hist ? c->d_export_hist : nullptr, dcap,
+  CU(c, launch_export(c->S, c->T, window_id, 1, c->d_export, hist ? c->d_export_hist : nullptr, dcap, 0,
                       c->d_owner_counts, c->d_owner_cursor, c->st_compute));
   CU(c, cudaMemcpyAsync(c->h_small, c->d_owner_counts, 8, cudaMemcpyDeviceToHost, c->st_compute));
   CU(c, cudaStreamSynchronize(c->st_compute));
@@ -585,13 +585,23 @@ int bh_decode_device(bh_ctx* c, const uint8_t* d_payload, const uint32_t* d_offs
 }
 
 int bh_export_window_device(bh_ctx* c, uint64_t window_id, uint32_t n_owners, bh_record* d_records,
-                            uint32_t* d_hist, uint64_t cap, uint64_t* d_owner_counts, void* stream) {
+                            uint32_t* d_hist, uint64_t cap, uint64_t owner_stride, uint64_t* d_owner_counts,
+                            void* stream) {
   if (!c || !d_records || !d_owner_counts) return fail(c, BH_ERR_INVALID, "null argument");
   if (!is_pow2(n_owners) || n_owners > 1024) return fail(c, BH_ERR_INVALID, "n_owners must be a power of two <= 1024");
+  if (owner_stride && owner_stride * n_owners > cap) return fail(c, BH_ERR_INVALID, "owner_stride * n_owners exceeds cap");
   DeviceGuard guard(c->device);
   cudaStream_t st = stream ? (cudaStream_t)stream : c->st_compute;
-  CU(c, launch_export(c->S, c->T, window_id, n_owners, d_records, d_hist, cap,
+  CU(c, launch_export(c->S, c->T, window_id, n_owners, d_records, d_hist, cap, owner_stride,
                       (unsigned long long*)d_owner_counts, c->d_owner_cursor, st));
+  return BH_OK;
+}
+
+int bh_reset_device(bh_ctx* c, void* stream) {
+  if (!c) return BH_ERR_INVALID;
+  DeviceGuard guard(c->device);
+  cudaStream_t st = stream ? (cudaStream_t)stream : c->st_compute;
+  CU(c, launch_init_tables(c->T, st));
   return BH_OK;
 }
 

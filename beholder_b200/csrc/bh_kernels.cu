@@ -497,41 +497,57 @@ __device__ __forceinline__ bool export_row(const DevTables& T, uint64_t base, ui
   return true;
 }
 
+// win == kNoWindow exports every open window.  Rows are visited ring slot by ring slot.
+__device__ __forceinline__ bool export_pick(const DevTables& T, uint64_t win, uint64_t row, uint64_t* base,
+                                            uint64_t* slot, uint64_t* row_win) {
+  uint32_t r = (uint32_t)(row / T.stride);
+  *slot = row - (uint64_t)r * T.stride;
+  *base = (uint64_t)r * T.stride;
+  unsigned long long w = T.ring_win[r];
+  *row_win = w;
+  return w != kNoWindow && (win == kNoWindow || w == win);
+}
+
 __global__ void k_export_count(const __grid_constant__ DevTables T, uint64_t win, uint32_t owner_shift,
                                unsigned long long* owner_counts) {
-  uint32_t r = (uint32_t)win & (T.ring - 1);
-  if (T.ring_win[r] != win) return;
-  uint64_t base = (uint64_t)r * T.stride;
-  for (uint64_t slot = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; slot < T.stride; slot += (uint64_t)gridDim.x * blockDim.x) {
-    uint64_t key;
+  uint64_t rows = (uint64_t)T.ring * T.stride, r0 = 0;
+  if (win != kNoWindow) { r0 = (uint64_t)((uint32_t)win & (T.ring - 1)) * T.stride; rows = r0 + T.stride; }
+  for (uint64_t row = r0 + blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; row < rows; row += (uint64_t)gridDim.x * blockDim.x) {
+    uint64_t base, slot, w, key;
+    if (!export_pick(T, win, row, &base, &slot, &w)) continue;
     if (!export_row(T, base, slot, &key)) continue;
     uint32_t o = owner_shift >= 64 ? 0u : (uint32_t)(key >> owner_shift);
     atomicAdd(&owner_counts[o], 1ull);
   }
 }
 
-__global__ void k_export_prefix(uint32_t n_owners, const unsigned long long* owner_counts, unsigned long long* cursor) {
+// cursor[o] = first output row of owner o: packed (exclusive prefix) or o * owner_stride
+__global__ void k_export_prefix(uint32_t n_owners, const unsigned long long* owner_counts, unsigned long long* cursor,
+                                uint64_t owner_stride) {
   if (blockIdx.x == 0 && threadIdx.x == 0) {
     unsigned long long acc = 0;
-    for (uint32_t o = 0; o < n_owners; o++) { cursor[o] = acc; acc += owner_counts[o]; }
+    for (uint32_t o = 0; o < n_owners; o++) {
+      cursor[o] = owner_stride ? (unsigned long long)o * owner_stride : acc;
+      acc += owner_counts[o];
+    }
   }
 }
 
 __global__ void k_export_scatter(const __grid_constant__ DevSchema S, const __grid_constant__ DevTables T, uint64_t win,
                                  uint32_t owner_shift, bh_record* out, uint32_t* hist_out, uint64_t cap,
-                                 unsigned long long* cursor) {
-  uint32_t r = (uint32_t)win & (T.ring - 1);
-  if (T.ring_win[r] != win) return;
-  uint64_t base = (uint64_t)r * T.stride;
-  for (uint64_t slot = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; slot < T.stride; slot += (uint64_t)gridDim.x * blockDim.x) {
-    uint64_t key;
+                                 unsigned long long* cursor, uint64_t owner_stride) {
+  uint64_t rows = (uint64_t)T.ring * T.stride, r0 = 0;
+  if (win != kNoWindow) { r0 = (uint64_t)((uint32_t)win & (T.ring - 1)) * T.stride; rows = r0 + T.stride; }
+  for (uint64_t row = r0 + blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; row < rows; row += (uint64_t)gridDim.x * blockDim.x) {
+    uint64_t base, slot, w, key;
+    if (!export_pick(T, win, row, &base, &slot, &w)) continue;
     if (!export_row(T, base, slot, &key)) continue;
     uint32_t o = owner_shift >= 64 ? 0u : (uint32_t)(key >> owner_shift);
     unsigned long long pos = atomicAdd(&cursor[o], 1ull);
-    if (pos >= cap) continue;
+    if (pos >= cap || (owner_stride && pos >= (unsigned long long)(o + 1) * owner_stride)) continue;
     const Stat s = T.stats[base + slot];
     bh_record rec;
-    rec.key_hash = key; rec.window_id = win; rec.count = s.count;
+    rec.key_hash = key; rec.window_id = w; rec.count = s.count;
     rec.sum = (S.ops & BH_OP_SUM) ? s.sum : 0.0;
     rec.min = (S.ops & BH_OP_MIN) && s.min_inv ? __longlong_as_double((long long)f64_unorder(~s.min_inv)) : 0.0;
     rec.max = (S.ops & BH_OP_MAX) && s.max_ord ? __longlong_as_double((long long)f64_unorder(s.max_ord)) : 0.0;
@@ -656,17 +672,18 @@ static uint32_t owner_shift_of(uint32_t n_owners) {
 }
 
 cudaError_t launch_export(const DevSchema& S, const DevTables& T, uint64_t window_id, uint32_t n_owners,
-                          bh_record* out, uint32_t* hist_out, uint64_t cap,
+                          bh_record* out, uint32_t* hist_out, uint64_t cap, uint64_t owner_stride,
                           unsigned long long* owner_counts, unsigned long long* owner_cursor,
                           cudaStream_t st) {
   cudaError_t e = cudaMemsetAsync(owner_counts, 0, sizeof(unsigned long long) * n_owners, st);
   if (e != cudaSuccess) return e;
   uint32_t shift = owner_shift_of(n_owners);
-  uint64_t blocks = (T.stride + 255) / 256;
+  uint64_t rows = window_id == kNoWindow ? (uint64_t)T.ring * T.stride : T.stride;
+  uint64_t blocks = (rows + 255) / 256;
   if (blocks > 148 * 8) blocks = 148 * 8;
   k_export_count<<<(uint32_t)blocks, 256, 0, st>>>(T, window_id, shift, owner_counts);
-  k_export_prefix<<<1, 32, 0, st>>>(n_owners, owner_counts, owner_cursor);
-  k_export_scatter<<<(uint32_t)blocks, 256, 0, st>>>(S, T, window_id, shift, out, hist_out, cap, owner_cursor);
+  k_export_prefix<<<1, 32, 0, st>>>(n_owners, owner_counts, owner_cursor, owner_stride);
+  k_export_scatter<<<(uint32_t)blocks, 256, 0, st>>>(S, T, window_id, shift, out, hist_out, cap, owner_cursor, owner_stride);
   return cudaGetLastError();
 }
 

@@ -23,7 +23,7 @@ cudaError_t launch_decode(const DevSchema& S, const LaunchGeom& G, const uint8_t
                           int32_t* status, uint8_t* outcome, cudaStream_t st);
 // compact one window into records grouped by owner (two passes: count, scatter)
 cudaError_t launch_export(const DevSchema& S, const DevTables& T, uint64_t window_id, uint32_t n_owners,
-                          bh_record* out, uint32_t* hist_out, uint64_t cap,
+                          bh_record* out, uint32_t* hist_out, uint64_t cap, uint64_t owner_stride,
                           unsigned long long* owner_counts, unsigned long long* owner_cursor,
                           cudaStream_t st);
 cudaError_t launch_merge(const DevSchema& S, const DevTables& T, const bh_record* recs,

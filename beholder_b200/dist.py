@@ -1,0 +1,88 @@
+"""Multi-GPU window close: key-hash sharded merge of per-window partial aggregates.
+
+One process per GPU (torch.distributed; NCCL over NVLink on the GPU box, gloo in the CPU tests).
+Events are spread over the ranks by arrival; every rank aggregates whatever keys it sees.  At
+window close each rank compacts its rows grouped by OWNER (owner = top log2(world) bits of the
+key hash), the ranks exchange rows with one fixed-size all-to-all, and each owner merges what it
+received into its own table: count/sum/hist add, min/max.  Integer results do not depend on
+the number of ranks; f64 sums differ by reduction order only.  The reference has no counterpart
+(it is a single Node process).
+"""
+from __future__ import annotations
+
+from typing import Optional
+
+import numpy as np
+
+RECORD_WORDS = 6   # bh_record = 6 x 8 bytes
+
+
+def owner_of(key_hash: np.ndarray, world: int) -> np.ndarray:
+    """owner rank of each key: its top log2(world) bits (world is a power of two)"""
+    lg = int(world).bit_length() - 1
+    assert 1 << lg == world, "world size must be a power of two"
+    if lg == 0:
+        return np.zeros(len(key_hash), dtype=np.int64)
+    return (key_hash.astype(np.uint64) >> np.uint64(64 - lg)).astype(np.int64)
+
+
+def partition_by_owner(records: np.ndarray, world: int, owner_stride: int) -> np.ndarray:
+    """Host mirror of bh_export_window_device(owner_stride > 0): a [world, owner_stride] array of
+    records, zero rows (count 0) as padding.  Raises if an owner has more rows than the stride."""
+    out = np.zeros((world, owner_stride), dtype=records.dtype)
+    own = owner_of(records["key_hash"], world)
+    for o in range(world):
+        rows = records[own == o]
+        if len(rows) > owner_stride:
+            raise ValueError(f"owner {o} has {len(rows)} rows > owner_stride {owner_stride}")
+        out[o, : len(rows)] = rows
+    return out
+
+
+def all_to_all_records(send, group=None):
+    """send: torch tensor [world, owner_stride, 6] int64 (device or CPU).  Row block o goes to rank o;
+    returns the blocks received from every rank, same shape."""
+    import torch
+    import torch.distributed as dist
+    recv = torch.empty_like(send)
+    if dist.get_world_size(group) == 1:
+        recv.copy_(send)
+        return recv
+    dist.all_to_all_single(recv.view(-1), send.view(-1), group=group)
+    return recv
+
+
+class WindowExchange:
+    """GPU side: export (grouped by owner) -> all-to-all over NCCL -> merge into the owner's table.
+
+    `local` aggregates this rank's share of the events; `owned` holds the merged rows of the keys
+    this rank owns.  All steps are enqueued on torch's current stream; nothing synchronises the host.
+    """
+
+    def __init__(self, local, owned, world: int, rank: int, owner_stride: int, device: int = 0):
+        import torch
+        self.local, self.owned, self.world, self.rank = local, owned, world, rank
+        self.owner_stride = owner_stride
+        dev = torch.device("cuda", device)
+        self.send = torch.zeros(world, owner_stride, RECORD_WORDS, dtype=torch.int64, device=dev)
+        self.counts = torch.zeros(world, dtype=torch.int64, device=dev)
+        self.kernel_launches_per_close = 3 + 1   # export (count, prefix, scatter) + merge
+
+    def close_all_windows(self, reset_local: bool = True):
+        import torch
+        from ._lib import BH_ALL_WINDOWS
+        st = torch.cuda.current_stream().cuda_stream
+        self.send.zero_()
+        self.local.export_window_device(BH_ALL_WINDOWS, self.world, self.send, None, self.world * self.owner_stride,
+                                        self.counts, owner_stride=self.owner_stride, stream=st)
+        recv = all_to_all_records(self.send)
+        self.owned.merge_records_device(recv, None, self.world * self.owner_stride, stream=st)
+        if reset_local:
+            self.local.reset_device(stream=st)
+        return recv
+
+    def check_no_overflow(self):
+        """host check (synchronises): no owner block was cut"""
+        c = self.counts.cpu().numpy()
+        if (c > self.owner_stride).any():
+            raise RuntimeError(f"owner_stride {self.owner_stride} too small: rows per owner {c.tolist()}")

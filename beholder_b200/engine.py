@@ -131,9 +131,12 @@ class Aggregator:
                                         _ptr(d_status), _ptr(d_outcome), stream or None))
 
     def export_window_device(self, window_id: int, n_owners: int, d_records, d_hist, cap: int, d_owner_counts,
-                             stream: int = 0) -> None:
+                             owner_stride: int = 0, stream: int = 0) -> None:
         self._ck(L.lib.bh_export_window_device(self._ctx, window_id, n_owners, _ptr(d_records), _ptr(d_hist), cap,
-                                               _ptr(d_owner_counts), stream or None))
+                                               owner_stride, _ptr(d_owner_counts), stream or None))
+
+    def reset_device(self, stream: int = 0) -> None:
+        self._ck(L.lib.bh_reset_device(self._ctx, stream or None))
 
     def merge_records_device(self, d_records, d_hist, n: int, stream: int = 0) -> None:
         self._ck(L.lib.bh_merge_records_device(self._ctx, _ptr(d_records), _ptr(d_hist), n, stream or None))

@@ -1,0 +1,396 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark of the beholder progress-event path on B200.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+    (N > 1: launched by the driver as `python -m torch.distributed.run --nproc-per-node N ... bench.py --gpus N ...`)
+
+Workload (BASELINE.json configs[1], "C2"): per GPU 100 M synthetic api.TelemetryProgress events of
+64 B, 1 000 distinct (mediaId, status) keys, 10 s tumbling windows, count/sum/min/max.  A step is one
+pass of the fused decode+aggregate kernel over those events (8 slabs of 12.5 M events = 8 launches),
+plus, at N > 1, the window-close exchange (export by owner -> NCCL all-to-all -> merge).
+
+`value`  : events/s, inputs resident in HBM, CUDA-event timed, max over ranks.
+`e2e`    : events/s through the C-ABI ingest (bh_push_batch_pinned -> bh_flush -> bh_snapshot): pinned
+           HOST buffers, H2D copies and the D2H read of the result inside the timed region.
+`roofline`: fused kernel, algorithmic bytes (payload + 4 B offset + 8 B timestamp per event) over its
+           average launch time, against the measured HBM copy bandwidth (MEASURED_PEAKS.json).
+`cpu_baseline`: the CPU oracle (a C restatement of the reference handler; Node and triton-core are
+           not available, so kind = "port") on the box's host cores, bounded sample.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "metric events/sec aggregated"
+UNIT = "events/s"
+EVENTS_PER_GPU = 100_000_000
+SLABS = 8
+PAYLOAD_BYTES = 64
+N_KEYS = 1000
+WINDOW_MS = 10_000
+BYTES_PER_EVENT = PAYLOAD_BYTES + 4 + 8      # S + u32 offset + u64 timestamp
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--events", type=int, default=EVENTS_PER_GPU, help="events per GPU per step")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    return ap.parse_args()
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def ncu_traffic():
+    p = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            return json.load(f).get("k_process_raw_dram_bytes_per_launch")
+    return None
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs"""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "200", "-i", str(self.index)], stdout=subprocess.PIPE, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if self.proc:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=5)
+            except Exception:
+                self.proc.kill()
+        sm, mx, reasons = [], 0, set()
+        for r in self.rows:
+            try:
+                sm.append(float(r[1])); mx = max(mx, float(r[2]))
+            except Exception:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx or None, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+def spec_for(rank: int, events: int):
+    from beholder_b200.synth import SynthSpec
+    rate = 500
+    # every rank covers the same stream time (round-robin delivery): shift t0 back by its index offset
+    first = rank * events
+    return SynthSpec(n_keys=N_KEYS, rate_per_ms=rate, jitter_ms=2000, payload_bytes=PAYLOAD_BYTES,
+                     t0_ms=1_700_000_000_000 - first // rate), first
+
+
+def generate_slabs(rank: int, events: int, device: int):
+    import torch
+    from beholder_b200.synth import generate_device
+    spec, first = spec_for(rank, events)
+    per = events // SLABS
+    slabs = []
+    for s in range(SLABS):
+        n = per if s < SLABS - 1 else events - per * (SLABS - 1)
+        p, o, t, total = generate_device(spec, first + s * per, n, device=device)
+        p = p[: (total + 15) // 16 * 16 + 16].clone()     # trim the generator's worst-case capacity
+        slabs.append((p, o, t, n, total))
+    torch.cuda.synchronize()
+    return slabs
+
+
+# ------------------------------------------------------------------------------------------
+# CPU legs (oracle port): cpu_baseline and --impl reference
+# ------------------------------------------------------------------------------------------
+def host_sample(events: int, device_ok: bool):
+    """one slab of the workload in host memory (numpy): from the device generator when a GPU is
+    there, else from the host build of the same generator (smaller)."""
+    import numpy as np
+    if device_ok:
+        import torch
+        from beholder_b200.synth import generate_device
+        spec, first = spec_for(0, EVENTS_PER_GPU)
+        p, o, t, total = generate_device(spec, first, events, device=0)
+        torch.cuda.synchronize()
+        return p[: total + 16].cpu().numpy(), o.cpu().numpy().view(np.uint32), t.cpu().numpy().view(np.uint64)
+    from beholder_b200.synth import generate_host
+    spec, first = spec_for(0, EVENTS_PER_GPU)
+    return generate_host(spec, first, events)
+
+
+def cpu_windowed(slab, off, ts, threads: int):
+    import beholder_b200 as bh
+    from beholder_b200 import _lib as L
+    from oracle import oracle as O
+    schema = bh.telemetry_progress().with_roles(key=("mediaId", "status"))
+    ops = L.OP_COUNT | L.OP_SUM | L.OP_MIN | L.OP_MAX
+    t0 = time.perf_counter()
+    a = O.Agg.run_threads(schema, ops, WINDOW_MS, 0xBE401DE5, slab, off, ts, threads)
+    dt = time.perf_counter() - t0
+    rows = len(a.snapshot())
+    return (len(off) - 1) / dt, rows
+
+
+def cpu_baseline_block(device_ok: bool):
+    import beholder_b200 as bh
+    from oracle import oracle as O
+    cores = os.cpu_count() or 1
+    n = 12_500_000 if device_ok else 200_000
+    slab, off, ts = host_sample(n, device_ok)
+    v_all, rows = cpu_windowed(slab, off, ts, cores)
+    m = min(n, 2_000_000)
+    v_one, _ = cpu_windowed(slab, off[: m + 1], ts[:m], 1)
+    out = {"value": v_all, "unit": UNIT, "cores": cores, "kind": "port",
+           "sample": f"{n} events = 1 of {SLABS} slabs of the C2 workload (windowed count/sum/min/max, oracle C port, "
+                     f"{cores} threads with private tables + merge); the reference itself (Node + triton-core) cannot run here",
+           "single_thread_value": v_one, "single_thread_sample_events": m, "rows": rows}
+    # the reference handler proper (count by status, index.js:127-155), 1 thread like Node, logger on/off
+    h = O.Handler(bh.telemetry_progress(), 0)
+    k = min(n, 2_000_000)
+    t0 = time.perf_counter(); O.run_handler_threads(bh.telemetry_progress(), slab, off[: k + 1], 1, 0); d0 = time.perf_counter() - t0
+    t0 = time.perf_counter(); O.run_handler_threads(bh.telemetry_progress(), slab, off[: k + 1], 1, 1); d1 = time.perf_counter() - t0
+    out["reference_handler_1thread_log_off"] = k / d0
+    out["reference_handler_1thread_log_on"] = k / d1
+    del h
+    return out
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU implementation of the path (the oracle port: Node and
+    triton-core are unavailable) on all host threads, same metric/config, bounded sample per step."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    try:
+        import torch
+        device_ok = torch.cuda.is_available()
+    except Exception:
+        device_ok = False
+    cores = os.cpu_count() or 1
+    n = 12_500_000 if device_ok else 200_000
+    slab, off, ts = host_sample(n, device_ok)
+    times = []
+    for i in range(args.warmup + args.steps):
+        t0 = time.perf_counter()
+        cpu_windowed(slab, off, ts, cores)
+        if i >= args.warmup:
+            times.append(time.perf_counter() - t0)
+    dt = sum(times) / len(times)
+    v = n / dt
+    sample = (f"each step = {n} events (1 of {SLABS} slabs of the C2 workload) through the oracle C port of "
+              f"index.js:127-155 + §B.2 on {cores} threads")
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "u64 counts / f64 sum,min,max", "data": "synthetic",
+        "config": workload_config(args.gpus),
+        "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+
+
+def workload_config(n_gpus: int):
+    return {"workload": f"C2: per GPU {EVENTS_PER_GPU} synthetic api.TelemetryProgress events x {PAYLOAD_BYTES} B, "
+                        f"{N_KEYS} distinct (mediaId,status) keys, {WINDOW_MS // 1000} s tumbling windows, count/sum/min/max, "
+                        f"raw protobuf payloads decoded on the GPU",
+            "events_per_gpu": EVENTS_PER_GPU, "slabs_per_step": SLABS, "payload_bytes": PAYLOAD_BYTES, "keys": N_KEYS,
+            "window_ms": WINDOW_MS, "ops": "count,sum,min,max", "key_distribution": "uniform",
+            "l2_policy": "inputs (7.6 GB per GPU per step) are larger than L2; no explicit flush",
+            "parallelism": f"events sharded over {n_gpus} GPU(s); key-hash owner merge per step (all-to-all) when N>1"}
+
+
+# ------------------------------------------------------------------------------------------
+# our arm
+# ------------------------------------------------------------------------------------------
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    import beholder_b200 as bh
+    from beholder_b200 import _lib as L
+    from beholder_b200.dist import WindowExchange
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        if world == 1 and args.gpus > 1:
+            raise SystemExit("--gpus N > 1 must be launched through torch.distributed.run (one rank per GPU)")
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: beholder_b200 has no CPU path")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    events = args.events
+    ops = L.OP_COUNT | L.OP_SUM | L.OP_MIN | L.OP_MAX
+    mk = lambda: bh.Aggregator(mode=L.MODE_WINDOWED, ops=ops, window_ms=WINDOW_MS, table_capacity=2048,  # noqa: E731
+                               window_ring=32, device=local_rank, slab_bytes=64 << 20, slab_events=1 << 20, n_slabs=4)
+    local = mk()
+    slabs = generate_slabs(rank, events, local_rank)
+    stream = torch.cuda.current_stream().cuda_stream
+    exch = None
+    if world > 1:
+        owned = mk()
+        exch = WindowExchange(local, owned, world, rank, owner_stride=2 * (N_KEYS * 40) // world, device=local_rank)
+
+    def step(ev_mid=None):
+        for p, o, t, n, _ in slabs:
+            local.process_device(p, o, t, n, stream=stream)
+        if ev_mid is not None:
+            ev_mid.record()
+        if exch is not None:
+            exch.close_all_windows(reset_local=True)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+    barrier()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+          for _ in range(args.steps)]
+    barrier()
+    e_start, e_end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e_start.record()
+    for a, m, b in ev:
+        a.record(); step(m); b.record()
+    e_end.record()
+    barrier()
+    clocks = sampler.stop() if rank == 0 else None
+    total_ms = e_start.elapsed_time(e_end)
+    kernel_ms = sum(a.elapsed_time(m) for a, m, _ in ev)
+    t = torch.tensor([total_ms, kernel_ms], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    total_ms, kernel_ms = t.tolist()
+    value = world * events * args.steps / (total_ms * 1e-3)
+
+    # correctness guard on what was just timed: every event counted exactly once
+    if exch is None:
+        k = local.counters()
+        done = max(args.warmup, 3) + args.steps
+        assert k["events_ok"] == events * done, (k, events * done)
+    else:
+        exch.check_no_overflow()
+        k = local.counters()
+        assert k["dropped_table_full"] == 0 and k["dropped_window"] == 0, k
+
+    # ---- end to end through the ingest C-ABI: pinned host buffers -> H2D -> kernel -> D2H result ----
+    e2e = None
+    if not args.no_e2e:
+        pins = []
+        for p, o, t_, n, total in slabs:
+            pb = bh.PinnedBuffer(p.numel()); ob = bh.PinnedBuffer((n + 1) * 4); tb = bh.PinnedBuffer(n * 8)
+            hp, ho, ht = pb.view(np.uint8), ob.view(np.uint32), tb.view(np.uint64)
+            torch.from_numpy(hp).copy_(p); torch.from_numpy(ho.view(np.int32)).copy_(o); torch.from_numpy(ht.view(np.int64)).copy_(t_)
+            pins.append((pb, ob, tb, hp, ho, ht, n, total))
+        torch.cuda.synchronize()
+        ing = mk()
+        h2d = sum(total + (n + 1) * 4 + n * 8 for *_, n, total in pins)
+
+        def e2e_step():
+            for _, _, _, hp, ho, ht, n, _ in pins:
+                ing.push_batch(hp, ho, ht, pinned=True)
+            ing.flush()
+            rows = 0
+            for w in ing.list_windows():
+                rows += len(ing.snapshot(w, cap=4096))
+            return rows
+
+        e2e_step()
+        barrier()
+        t0 = time.perf_counter()
+        e2e_steps = max(1, min(args.steps, 3))
+        rows = 0
+        for _ in range(e2e_steps):
+            rows = e2e_step()
+        barrier()
+        dt = time.perf_counter() - t0
+        tt = torch.tensor([dt], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        dt = tt.item()
+        k2 = ing.counters()
+        assert k2["events_ok"] == events * (e2e_steps + 1), k2
+        e2e = {"value": world * events * e2e_steps / dt, "unit": UNIT, "h2d_bytes_per_step": h2d,
+               "d2h_bytes_per_step": rows * 48 + 8 * 40, "steps": e2e_steps,
+               "path": "bh_push_batch_pinned -> (pinned host -> HBM in 64 MiB ring slabs on 2 copy streams) -> "
+                       "k_process_raw -> bh_flush -> bh_snapshot of every window",
+               "pcie_gbs": world * h2d * e2e_steps / dt / 1e9}
+        ing.close()
+        for pb, ob, tb, *_ in pins:
+            pb.free(); ob.free(); tb.free()
+
+    if rank == 0:
+        peak, peak_src = peaks()
+        launches_per_step = SLABS + (exch.kernel_launches_per_close + 5 if exch else 0)
+        per_launch_s = kernel_ms * 1e-3 / (args.steps * SLABS)
+        per_launch_bytes = sum(total + (n + 1) * 4 + n * 8 for *_, n, total in slabs) / SLABS
+        achieved = per_launch_bytes / per_launch_s / 1e9
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+            "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "u64 counts / f64 sum,min,max", "data": "synthetic", "config": workload_config(world),
+            "roofline": {"bound": "hbm", "kernel": "bh::k_process_raw", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                         "frac": achieved / peak, "traffic": ncu_traffic(), "peak_source": peak_src,
+                         "algorithmic_bytes_per_event": BYTES_PER_EVENT, "events_per_launch": events // SLABS,
+                         "avg_launch_ms": per_launch_s * 1e3},
+            "gpu_launches": launches_per_step * args.steps,
+            "clocks": clocks,
+        }
+        if e2e:
+            line["e2e"] = e2e
+        if world == 1 and not args.no_cpu:
+            line["cpu_baseline"] = cpu_baseline_block(True)
+        print(json.dumps(line))
+    local.close()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -151,11 +151,18 @@ int bh_process_columns_device(bh_ctx* ctx, const uint64_t* d_key_hash, const uin
 int bh_decode_device(bh_ctx* ctx, const uint8_t* d_payload, const uint32_t* d_offsets, uint32_t n,
                      uint64_t* d_key_hash, double* d_value, int32_t* d_status, uint8_t* d_outcome,
                      void* stream);
-/* compact one window into d_records grouped by owner = key_hash >> (64 - log2(n_owners)):
- * d_owner_counts[n_owners] receives rows per owner, rows of owner o start at sum(counts[<o]).
- * d_hist may be NULL.  No reference counterpart (the reference is one process). */
+/* compact one window (window_id = BH_ALL_WINDOWS: every open window) into d_records grouped by
+ * owner = key_hash >> (64 - log2(n_owners)).  d_owner_counts[n_owners] receives the rows each owner
+ * has.  owner_stride = 0: rows packed, owner o starts at sum(counts[<o]).  owner_stride > 0: owner o
+ * starts at o * owner_stride (fixed-size all-to-all; the caller zero-fills d_records first, rows with
+ * count 0 are padding; counts[o] > owner_stride means rows were cut).  d_hist may be NULL.
+ * No reference counterpart (the reference is one process). */
+#define BH_ALL_WINDOWS 0xFFFFFFFFFFFFFFFFull
 int bh_export_window_device(bh_ctx* ctx, uint64_t window_id, uint32_t n_owners, bh_record* d_records,
-                            uint32_t* d_hist, uint64_t cap, uint64_t* d_owner_counts, void* stream);
+                            uint32_t* d_hist, uint64_t cap, uint64_t owner_stride,
+                            uint64_t* d_owner_counts, void* stream);
+/* drop every window and zero the drop counters (the counters of index.js:32 "reset on restart") */
+int bh_reset_device(bh_ctx* ctx, void* stream);
 /* merge partial rows (from other GPUs) into this context's tables */
 int bh_merge_records_device(bh_ctx* ctx, const bh_record* d_records, const uint32_t* d_hist,
                             uint64_t n, void* stream);
