@@ -228,18 +228,21 @@ BH_HD void synth_event_fields(const bh_synth_config& c, uint64_t g, const uint64
 struct Emit {
   uint8_t* p;
   uint32_t n;
-  BH_HD void put(uint32_t b) { if (p) p[n] = (uint8_t)b; n++; }
+  uint32_t limit;   // bytes the event owns in the slab (a truncated event owns fewer than it emits)
+  BH_HD void put(uint32_t b) { if (p && n < limit) p[n] = (uint8_t)b; n++; }
   BH_HD void varint(uint32_t v) { while (v >= 128) { put((v & 127) | 128); v >>= 7; } put(v); }
 };
 
-// Builds (out != nullptr) or measures (out == nullptr) the wire bytes of event g.
-BH_HD uint32_t synth_build(const bh_synth_config& c, uint64_t g, const uint64_t* cdf, uint8_t* out, uint64_t* ts) {
+// Builds (out != nullptr, at most `limit` bytes written) or measures (out == nullptr) the wire bytes
+// of event g.
+BH_HD uint32_t synth_build(const bh_synth_config& c, uint64_t g, const uint64_t* cdf, uint8_t* out, uint64_t* ts,
+                           uint32_t limit) {
   SynthEvent e;
   synth_event_fields(c, g, cdf, e);
   if (ts) *ts = e.ts_ms;
   uint32_t status_len = e.status < 128 ? 1u : (e.status < 16384 ? 2u : 3u);
   uint32_t natural = 38 + 1 + status_len + (c.value_f64 ? 9u : 2u) + (e.host_len ? 2u + e.host_len : 0u);
-  Emit w{out, 0};
+  Emit w{out, 0, limit};
   w.put(0x0A); w.put(36);                                  // field 1 mediaId: string
   for (int i = 0; i < 36; i++) w.put((uint8_t)e.media_id[i]);
   if (c.payload_bytes && natural + 2 <= c.payload_bytes) { // field 15: ignored pad the decoder must skip
@@ -276,9 +279,13 @@ BH_HD uint32_t synth_build(const bh_synth_config& c, uint64_t g, const uint64_t*
     if ((r5 % 1000000u) < c.malformed_ppm) {
       switch ((r5 >> 40) & 3) {
         case 0: len = len / 2; break;                                        // truncated delivery
-        case 1: if (out) out[0] = 0x0F; break;                               // known field, wire type 7
-        case 2: if (out) out[e.host_len ? host_pos : value_pos] = e.host_len ? 0x4F : 0x4C; break;  // unknown field 9, wire type 7 / 4
-        default: if (out) out[status_pos + 1] |= 0x80; break;                // status varint runs on
+        case 1: if (out && limit) out[0] = 0x0F; break;                      // known field, wire type 7
+        case 2: {                                                            // unknown field 9, wire type 7 / 4
+          uint32_t at = e.host_len ? host_pos : value_pos;
+          if (out && at < limit) out[at] = e.host_len ? 0x4F : 0x4C;
+          break;
+        }
+        default: if (out && status_pos + 1 < limit) out[status_pos + 1] |= 0x80; break;   // status varint runs on
       }
     }
   }

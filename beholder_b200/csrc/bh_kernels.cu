@@ -373,7 +373,7 @@ __device__ __forceinline__ void raw_warp_loop(const DevSchema& S, const uint8_t*
       const uint32_t A = b0 & ~15u;
       const bool fits = valid && lane >= done && o1 >= o0 && o0 >= A && (o1 - A) <= kWarpBuf;
       uint32_t mask = __ballot_sync(0xFFFFFFFFu, fits) >> done;
-      uint32_t m = __ffs(~mask) - 1;   // leading run of lanes that fit
+      uint32_t m = mask == 0xFFFFFFFFu ? 32u : (uint32_t)__ffs(~mask) - 1u;   // leading run of lanes that fit
       uint32_t outcome; uint64_t kh; double value; uint32_t status;
       bool mine;
       if (m == 0) {                    // a single oversized (or inconsistent) message: parse from global
@@ -602,11 +602,12 @@ __global__ void k_close_release(const __grid_constant__ DevTables T, uint64_t wi
 // =========================================================================================
 // once per device, with that device current (bh_create)
 cudaError_t configure_kernels(const LaunchGeom& G) {
-  cudaError_t e = cudaFuncSetAttribute(k_process_raw, cudaFuncAttributeMaxDynamicSharedMemorySize, G.smem_optin);
+  int dyn = G.smem_optin - 1024;   // leave room for the kernels' static shared memory
+  cudaError_t e = cudaFuncSetAttribute(k_process_raw, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn);
   if (e != cudaSuccess) return e;
-  e = cudaFuncSetAttribute(k_decode, cudaFuncAttributeMaxDynamicSharedMemorySize, G.smem_optin);
+  e = cudaFuncSetAttribute(k_decode, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn);
   if (e != cudaSuccess) return e;
-  return cudaFuncSetAttribute(k_process_columns, cudaFuncAttributeMaxDynamicSharedMemorySize, G.smem_optin);
+  return cudaFuncSetAttribute(k_process_columns, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn);
 }
 
 static uint32_t pick_smem_slots(const DevTables& T, const LaunchGeom& G, size_t other_bytes) {

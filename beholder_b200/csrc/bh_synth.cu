@@ -13,7 +13,7 @@ __global__ void k_synth_sizes(const __grid_constant__ bh_synth_config c, uint64_
   for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i <= n; i += gridDim.x * blockDim.x) {
     if (i == n) { sizes[i] = 0; continue; }
     uint64_t t;
-    sizes[i] = synth_build(c, first + i, cdf, nullptr, &t);
+    sizes[i] = synth_build(c, first + i, cdf, nullptr, &t, 0xFFFFFFFFu);
     ts[i] = t;
   }
 }
@@ -22,7 +22,7 @@ __global__ void k_synth_build(const __grid_constant__ bh_synth_config c, uint64_
                               const uint64_t* __restrict__ cdf, const uint32_t* __restrict__ offsets,
                               uint8_t* payload) {
   for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
-    synth_build(c, first + i, cdf, payload + offsets[i], nullptr);
+    synth_build(c, first + i, cdf, payload + offsets[i], nullptr, offsets[i + 1] - offsets[i]);
 }
 
 __global__ void k_synth_columns(const __grid_constant__ bh_synth_config c, uint64_t hash_seed, uint64_t first,
@@ -61,11 +61,12 @@ uint32_t synth_max_event(const bh_synth_config& c) {
 extern "C" {
 
 uint32_t bh_synth_event_size(const bh_synth_config* c, uint64_t g, const uint64_t* zipf_cdf) {
-  return synth_build(*c, g, zipf_cdf, nullptr, nullptr);
+  return synth_build(*c, g, zipf_cdf, nullptr, nullptr, 0xFFFFFFFFu);
 }
 
 uint32_t bh_synth_event_host(const bh_synth_config* c, uint64_t g, const uint64_t* zipf_cdf, uint8_t* out, uint64_t* ts_ms) {
-  return synth_build(*c, g, zipf_cdf, out, ts_ms);
+  uint32_t len = synth_build(*c, g, zipf_cdf, nullptr, nullptr, 0xFFFFFFFFu);
+  return synth_build(*c, g, zipf_cdf, out, ts_ms, len);
 }
 
 int bh_synth_generate_device(int device, const bh_synth_config* c, uint64_t first, uint32_t n,

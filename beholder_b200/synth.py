@@ -106,6 +106,7 @@ def generate_device(spec: SynthSpec, first: int, n: int, device: int = 0, d_cdf=
     L.check(L.lib.bh_synth_generate_device(device, C.byref(c), first, n, d_cdf.data_ptr() if d_cdf is not None else None,
                                            payload.data_ptr(), payload.numel(), offsets.data_ptr(), ts.data_ptr(),
                                            C.byref(total), stream or None))
+    torch.cuda.current_stream(dev).synchronize()   # consumers may run on other (non-blocking) streams
     return payload, offsets, ts, int(total.value)
 
 
@@ -122,4 +123,5 @@ def columns_device(spec: SynthSpec, hash_seed: int, first: int, n: int, device: 
     L.check(L.lib.bh_synth_columns_device(device, C.byref(c), hash_seed, first, n,
                                           d_cdf.data_ptr() if d_cdf is not None else None,
                                           kh.data_ptr(), ts.data_ptr(), val.data_ptr(), stream or None))
+    torch.cuda.current_stream(dev).synchronize()
     return kh, ts, val

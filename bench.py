@@ -265,7 +265,12 @@ def main():
                                window_ring=32, device=local_rank, slab_bytes=64 << 20, slab_events=1 << 20, n_slabs=4)
     local = mk()
     slabs = generate_slabs(rank, events, local_rank)
-    stream = torch.cuda.current_stream().cuda_stream
+    # everything timed runs on ONE explicit torch stream: our launches (handle passed through the
+    # C-ABI), NCCL, and the CUDA events that time them
+    tstream = torch.cuda.Stream(device=local_rank)
+    torch.cuda.set_stream(tstream)
+    stream = tstream.cuda_stream
+    assert stream != 0
     exch = None
     if world > 1:
         owned = mk()

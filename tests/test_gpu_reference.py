@@ -139,7 +139,8 @@ def test_oversized_message_uses_global_path():
     ref = O.Handler(bh.telemetry_progress()); ref.handle_slab(slab, off)
     with bh.Aggregator(mode=L.MODE_REFERENCE) as g:
         g.push_batch(slab, off); g.flush()
-        assert g.status_counts() == ref.counts() == {"uploading": 2, "deployed": 3}
+        # the cut message keeps a clamped mediaId and no status -> proto3 default 0 -> "queued"
+        assert g.status_counts() == ref.counts() == {"queued": 1, "uploading": 1, "deployed": 3}
 
 
 def test_errors_are_reported_not_swallowed():

@@ -61,7 +61,8 @@ def test_histograms_and_spill_many_keys():
 
 @pytest.mark.parametrize("window_ms", [1, 7, 1000, 10_000, 4096, 86_400_000])
 def test_window_sizes(window_ms):
-    spec = SynthSpec(n_keys=50, rate_per_ms=3, jitter_ms=500)
+    # 667 ms of stream +- 500 ms jitter: ~240 windows of 7 ms (fits the ring), ~1700 of 1 ms (does not)
+    spec = SynthSpec(n_keys=50, rate_per_ms=30, jitter_ms=500)
     got, a, k = _run_raw(spec, 20_000, L.OP_COUNT | L.OP_SUM, window_ms=window_ms, table_capacity=256,
                          window_ring=1024 if window_ms < 100 else 32)
     if k["dropped_window"] == 0:
