@@ -77,30 +77,45 @@ int build_schema(const bh_config& cfg, DevSchema& S) {
   memset(&S, 0, sizeof S);
   uint32_t parts = 0;
   bool have_status = false;
+  S.int_values = 1;
+  S.fast_key0 = S.fast_status = S.fast_value = 0xFFFFFFFFu;
   for (uint32_t i = 0; i < cfg.n_fields; i++) {
     const bh_field& f = cfg.fields[i];
     if (f.number < 1 || f.number > BH_MAX_FIELD_NUMBER) return fail(nullptr, BH_ERR_UNSUPPORTED, "field number %u outside 1..%d", f.number, BH_MAX_FIELD_NUMBER);
     if (f.kind < BH_K_STRING || f.kind > BH_K_DOUBLE) return fail(nullptr, BH_ERR_UNSUPPORTED, "field %u: unsupported declared type %u", f.number, f.kind);
-    if (S.kind[f.number]) return fail(nullptr, BH_ERR_INVALID, "field %u declared twice", f.number);
-    S.kind[f.number] = (uint8_t)f.kind;
-    S.role[f.number] = (uint8_t)f.role;
+    if (S.fld[f.number]) return fail(nullptr, BH_ERR_INVALID, "field %u declared twice", f.number);
+    S.fld[f.number] = f.kind | ((f.role & 0xFFu) << 8);
     bool is_len = f.kind == BH_K_STRING || f.kind == BH_K_BYTES;
     if (f.role & BH_R_STATUS) {
       if (is_len || f.kind >= BH_K_FLOAT) return fail(nullptr, BH_ERR_INVALID, "status field %u must be a 32-bit varint type", f.number);
       have_status = true;
     }
     if ((f.role & BH_R_VALUE) && is_len) return fail(nullptr, BH_ERR_INVALID, "value field %u must be numeric", f.number);
+    if ((f.role & BH_R_VALUE) && !(f.kind == BH_K_INT32 || f.kind == BH_K_SINT32 || f.kind == BH_K_BOOL)) S.int_values = 0;
     if (f.role & BH_R_KEY) {
       if (f.kind == BH_K_FLOAT || f.kind == BH_K_DOUBLE) return fail(nullptr, BH_ERR_UNSUPPORTED, "key field %u: float keys not supported", f.number);
       if (parts >= BH_MAX_KEY_PARTS) return fail(nullptr, BH_ERR_UNSUPPORTED, "more than %d key fields", BH_MAX_KEY_PARTS);
-      S.part[f.number] = (uint8_t)(parts + 1);
+      S.fld[f.number] |= (parts + 1) << 16;
+      if (parts == 0 && f.kind == BH_K_STRING && f.role == BH_R_KEY) S.fast_key0 = f.number;
       S.part_field[parts] = (uint8_t)f.number;
       S.part_is_len[parts] = is_len;
       parts++;
     }
   }
+  for (uint32_t i = 0; i < cfg.n_fields; i++) {
+    const bh_field& f = cfg.fields[i];
+    if ((f.role & BH_R_STATUS) && !(f.role & BH_R_VALUE) && (f.kind == BH_K_INT32 || f.kind == BH_K_UINT32)) {
+      S.fast_status = f.number;
+      S.fast_status_part = (f.role & BH_R_KEY) ? (S.fld[f.number] >> 16) : 0;
+    }
+    if (f.role == BH_R_VALUE && (f.kind == BH_K_INT32 || f.kind == BH_K_DOUBLE)) {
+      S.fast_value = f.number;
+      S.fast_value_f64 = f.kind == BH_K_DOUBLE;
+    }
+  }
   S.n_parts = parts;
   S.mode = cfg.mode;
+  if (const char* d = getenv("BH_DEBUG_SKIP")) S.dbg = (uint32_t)atoi(d);
   if (cfg.mode == BH_MODE_REFERENCE) {
     if (!have_status) return fail(nullptr, BH_ERR_INVALID, "REFERENCE mode needs a field with BH_R_STATUS");
     S.status_part = 1;

@@ -91,9 +91,7 @@ BH_HD uint64_t div64(uint64_t n, const Div64& d) {
 // device-side view of the schema and the tables
 // ---------------------------------------------------------------------------------------
 struct DevSchema {
-  uint8_t kind[32];     // declared type by field number, 0 = unknown field
-  uint8_t role[32];
-  uint8_t part[32];     // key part index + 1
+  uint32_t fld[32];     // by field number: kind | role << 8 | (key part index + 1) << 16; 0 = unknown field
   uint8_t part_field[4];
   uint8_t part_is_len[4];
   uint32_t n_parts;
@@ -106,6 +104,14 @@ struct DevSchema {
   int32_t hist_e0;
   uint64_t hash_seed;
   uint32_t has_window;
+  uint32_t int_values;    // the VALUE field is int32 / sint32 / bool (or absent): integer shared-memory table
+  // fields the fast decoder recognises by number (0xFFFFFFFF = not applicable)
+  uint32_t fast_key0;        // key part 0 when it is a `string` with no other role
+  uint32_t fast_status;      // status when it is int32/uint32/enum (roles: status, optionally key)
+  uint32_t fast_status_part; // its key part index + 1, or 0
+  uint32_t fast_value;       // value when its only role is value and it is int32 or double
+  uint32_t fast_value_f64;   // ... and it is a double
+  uint32_t dbg;              // BH_DEBUG_SKIP (timing experiments): 1 no parse, 2 no hash, 4 no staging
   Div64 wdiv;
 };
 

@@ -1,14 +1,15 @@
 // bh_kernels.cu — sm_100a kernels of the beholder progress-event path.
 //
 //   k_process_raw      proto.decode + enumToString drop rule + counter update, fused
-//                      (index.js:129-138), one lane per message, payload staged per warp
-//                      through shared memory with 128-bit loads, shared-memory group-by table
-//                      in front of the HBM tables.
+//                      (index.js:129-138): one lane per message, a warp's batch of 32 messages is
+//                      staged through shared memory with coalesced 128-bit loads, a per-CTA
+//                      shared-memory group-by table sits in front of the HBM tables.
 //   k_process_columns  the counter update alone on pre-decoded columns (index.js:136-138).
 //   k_decode           proto.decode alone -> columns (index.js:129-134).
 //   k_export_* / k_merge / k_close_*   window close: compact, merge partials, recycle.
 //
-// Nothing here is a dense contraction: no tensor cores.  All kernels are HBM / L2-atomic bound.
+// Nothing here is a dense contraction: no tensor cores.  The kernels are bound by HBM bandwidth,
+// by instruction issue (the wire-format walk) or by L2 atomics (large key sets).
 #include "bh_kernels.cuh"
 
 namespace bh {
@@ -59,62 +60,87 @@ __device__ __forceinline__ void g_update(const DevTables& T, uint32_t ops, uint6
 
 // =========================================================================================
 // shared-memory front table (per CTA)
+//
+// Two layouts, chosen by the declared type of the reduced field:
+//   INTV  (int32 / sint32 / bool `progress`, the reference schema): sum as a 64-bit integer in two
+//         32-bit words, min / max as int32 -> every update is a NATIVE 32-bit shared atomic
+//         (ATOMS.ADD / ATOMS.MIN / ATOMS.MAX), no CAS loops, no divergence.  29 B per slot.
+//   F64   (double / float / uint32 values, and the columnar path): sum f64, min / max as
+//         order-preserving u64; shared memory has no native 64-bit add/max, the compiler's
+//         ATOMS.CAST.SPIN loops are used.  37 B per slot.
 // =========================================================================================
 struct SmemTable {
   unsigned long long* key;
-  double* sum;
-  unsigned long long* mn;   // ~order(min)
-  unsigned long long* mx;   //  order(max)
   uint32_t* cnt;
-  uint32_t* wrel;
-  uint32_t* gslot;
+  uint32_t* gslot;          // HBM slot of the entry; only when histograms are on (else nullptr)
+  uint8_t* wrel;            // window - wbase
+  void* va; void* vb; void* vc; void* vd;   // INTV: sum_lo u32, sum_hi i32, min i32, max i32 | F64: sum, -, min_inv, max_ord
   uint32_t ns;              // power of two
+  uint32_t shift;           // 32 - log2(ns)
 };
-constexpr uint32_t kSmemSlotBytes = 8 * 4 + 4 * 3;
-constexpr int kSmemProbes = 12;
+constexpr int kSmemProbes = 16;
+constexpr uint32_t kWrelUnset = 0xFFu;   // window byte of a claimed slot that its owner has not filled in yet
+__host__ __device__ constexpr uint32_t smem_slot_bytes(bool intv, bool hist) {
+  return 8 + (intv ? 16 : 24) + 4 + 1 + (hist ? 4 : 0);
+}
 
-__device__ __forceinline__ SmemTable smem_table_carve(uint8_t* base, uint32_t ns) {
+template <bool INTV>
+__device__ __forceinline__ SmemTable smem_table_carve(uint8_t* base, uint32_t ns, bool hist) {
   SmemTable M;
   M.key = (unsigned long long*)base;
-  M.sum = (double*)(base + (size_t)ns * 8);
-  M.mn = (unsigned long long*)(base + (size_t)ns * 16);
-  M.mx = (unsigned long long*)(base + (size_t)ns * 24);
-  M.cnt = (uint32_t*)(base + (size_t)ns * 32);
-  M.wrel = M.cnt + ns;
-  M.gslot = M.wrel + ns;
+  uint8_t* p = base + (size_t)ns * 8;
+  if (INTV) { M.va = p; M.vb = p + (size_t)ns * 4; M.vc = p + (size_t)ns * 8; M.vd = p + (size_t)ns * 12; p += (size_t)ns * 16; }
+  else { M.va = p; M.vb = nullptr; M.vc = p + (size_t)ns * 8; M.vd = p + (size_t)ns * 16; p += (size_t)ns * 24; }
+  M.cnt = (uint32_t*)p; p += (size_t)ns * 4;
+  M.gslot = hist ? (uint32_t*)p : nullptr; if (hist) p += (size_t)ns * 4;
+  M.wrel = p;
   M.ns = ns;
+  M.shift = 32u - (31u - (uint32_t)__clz((int)ns));
   return M;
 }
 
+template <bool INTV>
 __device__ __forceinline__ void smem_table_clear(const SmemTable& M) {
   for (uint32_t i = threadIdx.x; i < M.ns; i += blockDim.x) {
-    M.key[i] = kEmptyKey; M.sum[i] = 0.0; M.mn[i] = 0; M.mx[i] = 0; M.cnt[i] = 0; M.wrel[i] = 0; M.gslot[i] = 0;
+    M.key[i] = kEmptyKey; M.cnt[i] = 0; M.wrel[i] = (uint8_t)kWrelUnset;
+    if (M.gslot) M.gslot[i] = 0;
+    if (INTV) {
+      ((uint32_t*)M.va)[i] = 0; ((int32_t*)M.vb)[i] = 0;
+      ((int32_t*)M.vc)[i] = 0x7FFFFFFF; ((int32_t*)M.vd)[i] = (int32_t)0x80000000;
+    } else {
+      ((double*)M.va)[i] = 0.0; ((unsigned long long*)M.vc)[i] = 0; ((unsigned long long*)M.vd)[i] = 0;
+    }
   }
 }
 
-// returns the shared slot, or -1 when the event has to go to the HBM table directly
+// returns the shared slot, or -1 when the event has to go to the HBM table directly.
+// Claiming a slot is ONE compare-and-swap on the key word (empty -> key); the window byte follows with a
+// plain store and readers that match the key wait for it (0xFF = not written yet).  No fence is needed:
+// only the one location is polled.  With histograms on, the HBM slot must be visible before the window
+// byte, which costs a block-level fence on that (rare) path only.
+__device__ uint32_t g_dbg_probes;
 __device__ __forceinline__ int smem_find_or_insert(const SmemTable& M, const DevTables& T, uint64_t kh,
-                                                   uint32_t wrel, uint64_t win) {
-  uint32_t slot = (uint32_t)(((kh ^ ((uint64_t)wrel * 0xD6E8FEB86659FD93ull)) * kHashMul) >> 32) & (M.ns - 1);
+                                                   uint32_t wrel, uint64_t win, uint32_t* probes = nullptr) {
+  uint32_t x = (uint32_t)kh ^ (uint32_t)(kh >> 32) ^ (wrel * 0x85EBCA6Bu);
+  uint32_t slot = (x * 0x9E3779B1u) >> M.shift;
   volatile unsigned long long* vkey = M.key;
-  volatile uint32_t* vwrel = M.wrel;
+  volatile uint8_t* vwrel = M.wrel;
 #pragma unroll 1
   for (int p = 0; p < kSmemProbes; p++) {
+    if (probes) (*probes)++;
     unsigned long long k = vkey[slot];
-    if (k == kh) {
-      if (vwrel[slot] == wrel) return (int)slot;
-    } else if (k == kEmptyKey) {
-      unsigned long long old = atomicCAS(&M.key[slot], (unsigned long long)kEmptyKey, (unsigned long long)kLockKey);
-      if (old == kEmptyKey) {   // claimed: resolve the HBM slot once, then publish
-        uint32_t r;
-        uint32_t gs = g_find_or_insert(T, win, kh, &r);
-        M.gslot[slot] = gs;
-        vwrel[slot] = wrel;
-        __threadfence_block();
-        vkey[slot] = kh;
+    if (k == kEmptyKey) {
+      k = atomicCAS(&M.key[slot], (unsigned long long)kEmptyKey, (unsigned long long)kh);
+      if (k == kEmptyKey) {     // claimed
+        if (M.gslot) { uint32_t r; M.gslot[slot] = g_find_or_insert(T, win, kh, &r); __threadfence_block(); }
+        vwrel[slot] = (uint8_t)wrel;
         return (int)slot;
       }
-      if (old == kh && vwrel[slot] == wrel) return (int)slot;
+    }
+    if (k == kh) {
+      uint32_t w = vwrel[slot];
+      while (w == kWrelUnset) w = vwrel[slot];
+      if (w == wrel) return (int)slot;
     }
     slot = (slot + 1) & (M.ns - 1);
   }
@@ -127,52 +153,97 @@ struct LaneCounters {
 #pragma unroll
     for (int i = 0; i < 7; i++) c[i] = 0;
   }
+  __device__ __forceinline__ void bump(uint32_t which) {   // keeps c[] in registers
+#pragma unroll
+    for (int i = 0; i < 7; i++) c[i] += (which == (uint32_t)i);
+  }
 };
 
 // One event into the tables.  `wbase` is the CTA's first window minus one.
+// INTV: `iv` is the value; otherwise `v`.
+template <bool INTV>
 __device__ __forceinline__ void aggregate_event(const DevSchema& S, const DevTables& T, const SmemTable& M,
-                                                uint64_t kh, uint64_t win, uint64_t wbase, double v,
+                                                uint64_t kh, uint64_t win, uint64_t wbase, double v, int32_t iv,
                                                 LaneCounters& C) {
   const uint32_t ops = S.ops;
-  uint64_t bits = (uint64_t)__double_as_longlong(v);
-  uint64_t ord = f64_order(bits);
-  uint64_t wr = win - wbase;
+  const uint64_t wr = win - wbase;
   int slot = -1;
-  if (kh < kLockKey && wr < 0xFFFFFFFFull && M.ns) slot = smem_find_or_insert(M, T, kh, (uint32_t)wr, win);
+  if (S.dbg & 16) slot = (int)((((uint32_t)kh ^ (uint32_t)(kh >> 32)) * 0x9E3779B1u) >> M.shift);
+  else if (S.dbg & 32) { uint32_t pr = 0; slot = smem_find_or_insert(M, T, kh, (uint32_t)wr, win, &pr); C.c[C_SPILL] += pr; }
+  else if (kh < kLockKey && wr < 255ull) slot = smem_find_or_insert(M, T, kh, (uint32_t)wr, win);
+  if (S.dbg & 8) { C.c[C_OK] += (slot >= 0); return; }
   if (slot >= 0) {
-    uint32_t gs = M.gslot[slot];
-    if (gs >= kGslotWindow) { C.c[gs == kGslotFull ? C_TABLE_FULL : C_WINDOW]++; return; }
-    atomicAdd(&M.cnt[slot], 1u);
-    if (ops & BH_OP_SUM) atomicAdd(&M.sum[slot], v);
-    if ((ops & BH_OP_MIN) && ~ord > M.mn[slot]) atomicMax(&M.mn[slot], (unsigned long long)~ord);
-    if ((ops & BH_OP_MAX) && ord > M.mx[slot]) atomicMax(&M.mx[slot], (unsigned long long)ord);
     if (ops & BH_OP_HIST) {
+      if (INTV) v = (double)iv;
+      uint32_t gs = M.gslot[slot];
+      if (gs >= kGslotWindow) { C.bump(gs == kGslotFull ? C_TABLE_FULL : C_WINDOW); return; }
       uint64_t gi = (uint64_t)((uint32_t)win & (T.ring - 1)) * T.stride + gs;
-      atomicAdd(&T.hist[gi * T.hist_buckets + hist_bucket(bits, T.hist_buckets, S.hist_e0)], 1u);
+      atomicAdd(&T.hist[gi * T.hist_buckets + hist_bucket((uint64_t)__double_as_longlong(v), T.hist_buckets, S.hist_e0)], 1u);
+    }
+    atomicAdd(&M.cnt[slot], 1u);
+    if (INTV) {
+      if (ops & BH_OP_SUM) {
+        const uint32_t add = (uint32_t)iv;
+        const uint32_t old = atomicAdd((uint32_t*)M.va + slot, add);
+        const int32_t hi = (iv >> 31) + (int32_t)(old + add < old);   // sign extension + carry
+        if (hi) atomicAdd((int32_t*)M.vb + slot, hi);
+      }
+      if (ops & BH_OP_MIN) atomicMin((int32_t*)M.vc + slot, iv);
+      if (ops & BH_OP_MAX) atomicMax((int32_t*)M.vd + slot, iv);
+    } else {
+      const uint64_t ord = f64_order((uint64_t)__double_as_longlong(v));
+      if (ops & BH_OP_SUM) atomicAdd((double*)M.va + slot, v);
+      if (ops & BH_OP_MIN) atomicMax((unsigned long long*)M.vc + slot, (unsigned long long)~ord);
+      if (ops & BH_OP_MAX) atomicMax((unsigned long long*)M.vd + slot, (unsigned long long)ord);
     }
     C.c[C_OK]++;
     return;
   }
   // spill: straight to the HBM table
+  if (INTV) v = (double)iv;
+  const uint64_t bits = (uint64_t)__double_as_longlong(v);
+  const uint64_t ord = f64_order(bits);
   uint32_t r;
   uint32_t gs = g_find_or_insert(T, win, kh, &r);
-  if (gs >= kGslotWindow) { C.c[gs == kGslotFull ? C_TABLE_FULL : C_WINDOW]++; return; }
+  if (gs >= kGslotWindow) { C.bump(gs == kGslotFull ? C_TABLE_FULL : C_WINDOW); return; }
   uint64_t gi = (uint64_t)r * T.stride + gs;
   g_update(T, ops, gi, 1ull, v, ~ord, ord);
   if (ops & BH_OP_HIST) atomicAdd(&T.hist[gi * T.hist_buckets + hist_bucket(bits, T.hist_buckets, S.hist_e0)], 1u);
   C.c[C_OK]++; C.c[C_SPILL]++;
 }
 
+// CTA end: every shared entry goes to its HBM slot.  Events of an entry whose window or key cannot
+// be placed move from the "ok" counter to the drop counter that explains them.
+template <bool INTV>
 __device__ __forceinline__ void smem_table_flush(const DevSchema& S, const DevTables& T, const SmemTable& M, uint64_t wbase) {
-  for (uint32_t i = threadIdx.x; i < M.ns; i += blockDim.x) {
+  // every CTA hashes a key to the same shared slot: rotate the scan by CTA so that the CTAs do not all
+  // hit the same HBM entry at the same moment (same-address L2 atomics serialise)
+  const uint32_t rot = (blockIdx.x * 0x9E3779B1u) >> M.shift;
+  for (uint32_t j = threadIdx.x; j < M.ns; j += blockDim.x) {
+    const uint32_t i = (j + rot) & (M.ns - 1);
     unsigned long long k = M.key[i];
     uint32_t c = M.cnt[i];
     if (k == kEmptyKey || c == 0) continue;
-    uint32_t gs = M.gslot[i];
-    if (gs >= kGslotWindow) continue;
     uint64_t win = wbase + M.wrel[i];
-    uint64_t gi = (uint64_t)((uint32_t)win & (T.ring - 1)) * T.stride + gs;
-    g_update(T, S.ops, gi, c, M.sum[i], M.mn[i], M.mx[i]);
+    uint32_t r = (uint32_t)win & (T.ring - 1);
+    uint32_t gs = M.gslot ? M.gslot[i] : g_find_or_insert(T, win, k, &r);
+    if (gs >= kGslotWindow) {
+      if (!M.gslot) {   // (with histograms on, the event was already refused when it arrived)
+        atomicAdd(&T.counters[gs == kGslotFull ? C_TABLE_FULL : C_WINDOW], (unsigned long long)c);
+        atomicAdd(&T.counters[C_OK], 0ull - (unsigned long long)c);
+      }
+      continue;
+    }
+    double sum; unsigned long long mn_inv, mx_ord;
+    if (INTV) {
+      long long s64 = (long long)(((unsigned long long)(uint32_t)((int32_t*)M.vb)[i] << 32) | ((uint32_t*)M.va)[i]);
+      sum = (double)s64;
+      mn_inv = ~f64_order((uint64_t)__double_as_longlong((double)((int32_t*)M.vc)[i]));
+      mx_ord = f64_order((uint64_t)__double_as_longlong((double)((int32_t*)M.vd)[i]));
+    } else {
+      sum = ((double*)M.va)[i]; mn_inv = ((unsigned long long*)M.vc)[i]; mx_ord = ((unsigned long long*)M.vd)[i];
+    }
+    g_update(T, S.ops, (uint64_t)r * T.stride + gs, c, sum, mn_inv, mx_ord);
   }
 }
 
@@ -186,20 +257,29 @@ __device__ __forceinline__ void counters_flush(const DevTables& T, LaneCounters&
   if (threadIdx.x < 7 && s_cnt[threadIdx.x]) atomicAdd(&T.counters[threadIdx.x], (unsigned long long)s_cnt[threadIdx.x]);
 }
 
+// shared-memory access by 32-bit shared-window address, for the staged payload bytes
+__device__ __forceinline__ uint32_t lds8(uint32_t a) { uint32_t v; asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(a)); return v; }
+__device__ __forceinline__ uint32_t lds32(uint32_t a) { uint32_t v; asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a)); return v; }
+__device__ __forceinline__ void sts32(uint32_t a, uint32_t v) { asm volatile("st.shared.u32 [%0], %1;" :: "r"(a), "r"(v) : "memory"); }
+
 // =========================================================================================
 // protobufjs 6.8.8 reader semantics on the device (what proto.decode does, index.js:129)
 // =========================================================================================
-struct SmemRd {           // event bytes staged in shared memory; 16 B of slack after the batch
-  const uint8_t* p;
-  __device__ __forceinline__ uint32_t b(uint32_t i) const { return p[i]; }
+// A warp's batch is staged in shared memory SKEWED: 4 bytes of padding after every 64, so that 32
+// lanes walking 64-byte messages in lock step hit 32 different banks (stride 17 words) instead of 2.
+__device__ __forceinline__ uint32_t skew(uint32_t a) { return a + ((a >> 6) << 2); }
+
+struct SmemRd {           // event bytes staged (skewed) in shared memory
+  uint32_t base;          // shared-window address of the warp buffer
+  uint32_t off;           // logical offset of this event's first byte in the buffer
+  __device__ __forceinline__ uint32_t b(uint32_t i) const { return lds8(base + skew(off + i)); }
+  __device__ __forceinline__ uint32_t ab(uint32_t lp) const { return lds8(base + skew(lp)); }   // absolute logical position
+  __device__ __forceinline__ uint32_t w32(uint32_t a) const { return lds32(base + skew(a)); }   // aligned logical word
   __device__ __forceinline__ uint64_t le64(uint32_t i, uint32_t nvalid) const {
-    uint32_t a = (uint32_t)__cvta_generic_to_shared(p + i);
+    uint32_t a = off + i;
     uint32_t sh = (a & 3u) * 8u;
     a &= ~3u;
-    uint32_t w0, w1, w2;
-    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(w0) : "r"(a));
-    asm volatile("ld.shared.u32 %0, [%1+4];" : "=r"(w1) : "r"(a));
-    asm volatile("ld.shared.u32 %0, [%1+8];" : "=r"(w2) : "r"(a));
+    uint32_t w0 = w32(a), w1 = w32(a + 4), w2 = w32(a + 8);
     uint32_t lo = __funnelshift_r(w0, w1, sh), hi = __funnelshift_r(w1, w2, sh);
     uint64_t w = ((uint64_t)hi << 32) | lo;
     return nvalid >= 8 ? w : (w & ((1ull << (8 * nvalid)) - 1));
@@ -218,9 +298,9 @@ struct GmemRd {           // slow path: event parsed straight from global memory
 // Reader.uint32(): 5 value bytes; a longer varint is assumed to be 10 bytes; bytes past the end read
 // as `undefined` (no value bits, "continue").
 template <class R>
-__device__ __forceinline__ bool rd_uint32(const R& r, uint32_t& pos, uint32_t len, uint32_t& out) {
+__device__ __noinline__ bool rd_uint32(const R& r, uint32_t& pos, uint32_t len, uint32_t& out) {
   uint32_t v = 0;
-#pragma unroll
+#pragma unroll 1
   for (int i = 0; i < 5; i++) {
     uint32_t byte = pos < len ? r.b(pos) : 0x80u;
     pos++;
@@ -258,53 +338,64 @@ __device__ __forceinline__ bool rd_skip_type(const R& r, uint32_t& pos, uint32_t
 
 struct Parsed {
   uint32_t status;
-  double value;
+  uint32_t uval;      // VALUE field as decoded 32-bit integer (varint kinds)
+  double value;       // VALUE field as a JS number (not filled by the fast path for integer kinds)
   uint32_t ppos[BH_MAX_KEY_PARTS], plen[BH_MAX_KEY_PARTS], pval[BH_MAX_KEY_PARTS];
+  __device__ __forceinline__ void clear() {
+    status = 0; uval = 0; value = 0.0;
+#pragma unroll
+    for (int k = 0; k < BH_MAX_KEY_PARTS; k++) { ppos[k] = 0; plen[k] = 0; pval[k] = 0; }
+  }
 };
 
-// Type.decode(): known fields are read by DECLARED type whatever the wire type; string() on a Node
-// Buffer clamps to the end, bytes() throws.  Returns false where proto.decode would throw.
+// One known field read by its DECLARED type (protobufjs' generated decoder ignores the wire type),
+// result stored by role.  string() on a Node Buffer clamps to the end, bytes() throws.
 template <class R>
-__device__ __forceinline__ bool decode_event(const DevSchema& S, const R& r, uint32_t len, Parsed& P) {
-  P.status = 0; P.value = 0.0;
+__device__ __forceinline__ bool decode_known_field(const R& r, uint32_t f, uint32_t& pos, uint32_t len, Parsed& P) {
+  const uint32_t kind = f & 0xFFu, role = (f >> 8) & 0xFFu;
+  uint32_t u = 0, spos = 0, slen = 0;
+  double num = 0.0;
+  if (kind <= BH_K_BYTES) {
+    uint32_t n;
+    if (!rd_uint32(r, pos, len, n)) return false;
+    uint64_t end = (uint64_t)pos + n;
+    if (end > len) { if (kind == BH_K_BYTES) return false; end = len; }
+    spos = pos; slen = (uint32_t)end - pos; pos = (uint32_t)end;
+  } else if (kind <= BH_K_BOOL) {
+    if (!rd_uint32(r, pos, len, u)) return false;
+    if (kind == BH_K_SINT32) u = (u >> 1) ^ (0u - (u & 1u));
+    else if (kind == BH_K_BOOL) u = u != 0;
+    num = kind == BH_K_UINT32 || kind == BH_K_BOOL ? (double)u : (double)(int32_t)u;
+  } else if (kind == BH_K_FLOAT) {
+    if ((uint64_t)pos + 4 > len) return false;
+    num = (double)__uint_as_float((uint32_t)r.le64(pos, 4)); pos += 4;
+  } else {
+    if ((uint64_t)pos + 8 > len) return false;
+    num = __longlong_as_double((long long)r.le64(pos, 8)); pos += 8;
+  }
+  if (role & BH_R_STATUS) P.status = u;
+  if (role & BH_R_VALUE) { P.value = num; P.uval = u; }
+  if (role & BH_R_KEY) {
+    const uint32_t part = f >> 16;
 #pragma unroll
-  for (int k = 0; k < BH_MAX_KEY_PARTS; k++) { P.ppos[k] = 0; P.plen[k] = 0; P.pval[k] = 0; }
+    for (int k = 0; k < BH_MAX_KEY_PARTS; k++)
+      if (part == (uint32_t)k + 1) { P.ppos[k] = spos; P.plen[k] = slen; P.pval[k] = u; }
+  }
+  return true;
+}
+
+// Type.decode(), complete.  Returns false where proto.decode would throw.
+template <class R>
+__device__ __noinline__ bool decode_event(const DevSchema& S, const R& r, uint32_t len, Parsed& P) {
+  P.clear();
   uint32_t pos = 0;
   while (pos < len) {
     uint32_t t;
     if (!rd_uint32(r, pos, len, t)) return false;
-    uint32_t fn = t >> 3;
-    uint32_t kind = fn < 32 ? S.kind[fn] : 0;
-    if (kind == 0) { if (!rd_skip_type(r, pos, len, t & 7u)) return false; continue; }
-    uint32_t role = S.role[fn];
-    uint32_t u = 0, spos = 0, slen = 0;
-    double num = 0.0;
-    if (kind <= BH_K_BYTES) {
-      uint32_t n;
-      if (!rd_uint32(r, pos, len, n)) return false;
-      uint64_t end = (uint64_t)pos + n;
-      if (end > len) { if (kind == BH_K_BYTES) return false; end = len; }
-      spos = pos; slen = (uint32_t)end - pos; pos = (uint32_t)end;
-    } else if (kind <= BH_K_BOOL) {
-      if (!rd_uint32(r, pos, len, u)) return false;
-      if (kind == BH_K_SINT32) u = (u >> 1) ^ (0u - (u & 1u));
-      else if (kind == BH_K_BOOL) u = u != 0;
-      num = kind == BH_K_UINT32 || kind == BH_K_BOOL ? (double)u : (double)(int32_t)u;
-    } else if (kind == BH_K_FLOAT) {
-      if ((uint64_t)pos + 4 > len) return false;
-      num = (double)__uint_as_float((uint32_t)r.le64(pos, 4)); pos += 4;
-    } else {
-      if ((uint64_t)pos + 8 > len) return false;
-      num = __longlong_as_double((long long)r.le64(pos, 8)); pos += 8;
-    }
-    if (role & BH_R_STATUS) P.status = u;
-    if (role & BH_R_VALUE) P.value = num;
-    if (role & BH_R_KEY) {
-      uint32_t part = S.part[fn];
-#pragma unroll
-      for (int k = 0; k < BH_MAX_KEY_PARTS; k++)
-        if (part == (uint32_t)k + 1) { P.ppos[k] = spos; P.plen[k] = slen; P.pval[k] = u; }
-    }
+    const uint32_t fn = t >> 3;
+    const uint32_t f = fn < 32 ? S.fld[fn] : 0;
+    if ((f & 0xFFu) == 0) { if (!rd_skip_type(r, pos, len, t & 7u)) return false; continue; }
+    if (!decode_known_field(r, f, pos, len, P)) return false;
   }
   return true;
 }
@@ -328,99 +419,278 @@ __device__ __forceinline__ uint64_t event_key_hash(const DevSchema& S, const R& 
   return fmix64(h);
 }
 
-// decode + drop rules of one event.  Returns BH_EV_*.
-template <class R>
-__device__ __forceinline__ uint32_t decode_and_check(const DevSchema& S, const R& r, uint32_t len, uint64_t& kh,
-                                                     double& value, uint32_t& status) {
-  Parsed P;
-  if (!decode_event(S, r, len, P)) { kh = 0; value = 0.0; status = 0; return BH_EV_DROP_DECODE; }
-  kh = event_key_hash(S, r, P);
-  value = P.value; status = P.status;
+// ---- fast path ---------------------------------------------------------------------------------
+// Messages whose tags, lengths and varints are single bytes (two for the length of an unknown
+// length-delimited field) — what well-formed api.TelemetryProgress events look like.  The three hot
+// fields (first length-delimited key part, status, value) are recognised by comparing the field
+// number with launch constants; every other field goes through the schema table.  Anything unusual
+// makes it return false and the event is re-parsed by decode_event, so the outcome is decode_event's
+// in every case; the fast path only has to agree with it on the inputs it accepts.
+__device__ __forceinline__ bool decode_fast(const DevSchema& S, const SmemRd& r, uint32_t len, Parsed& P) {
+  P.clear();
+  uint32_t lp = r.off;
+  const uint32_t end = r.off + len;
+  while (lp < end) {
+    if (lp + 2 > end) return false;
+    const uint32_t t = r.ab(lp), b1 = r.ab(lp + 1);
+    lp += 2;
+    if (t & 0x80u) return false;
+    const uint32_t fn = t >> 3;
+    if (fn == S.fast_key0) {                 // string key part 0 (mediaId)
+      if (b1 & 0x80u) return false;
+      uint32_t e2 = lp + b1;
+      e2 = e2 > end ? end : e2;              // BufferReader.string() clamps
+      P.ppos[0] = lp - r.off; P.plen[0] = e2 - lp; lp = e2;
+      continue;
+    }
+    if (fn == S.fast_status) {               // int32 / enum status, possibly also a key part
+      if (b1 & 0x80u) return false;
+      P.status = b1;
+      if (S.fast_status_part == 1) P.pval[0] = b1;
+      if (S.fast_status_part == 2) P.pval[1] = b1;
+      if (S.fast_status_part == 3) P.pval[2] = b1;
+      continue;
+    }
+    if (fn == S.fast_value) {                // int32 value as a one-byte varint, or a double
+      if (S.fast_value_f64) {
+        if (lp + 7 > end) return false;
+        P.value = __longlong_as_double((long long)r.le64(lp - 1 - r.off, 8)); lp += 7;
+      } else {
+        if (b1 & 0x80u) return false;
+        P.uval = b1;
+      }
+      continue;
+    }
+    const uint32_t f = S.fld[fn];
+    if ((f & 0xFFu) == 0) {                  // unknown field: Reader.skipType
+      const uint32_t wt = t & 7u;
+      if (wt == 2) {
+        uint32_t n = b1;
+        if (b1 & 0x80u) {                    // two-byte length (pads of 128 B .. 16 KB)
+          if (lp >= end) return false;
+          const uint32_t b2 = r.ab(lp);
+          if (b2 & 0x80u) return false;
+          n = (b1 & 0x7Fu) | (b2 << 7);
+          lp += 1;
+        }
+        if (lp + n > end) return false;      // decode_event will report the throw
+        lp += n;
+      } else if (wt == 0) {
+        if (b1 & 0x80u) return false;
+      } else {
+        return false;
+      }
+      continue;
+    }
+    // other known fields (host, further key parts, ...): declared-type read through the table
+    if (b1 & 0x80u) return false;
+    const uint32_t kind = f & 0xFFu;
+    if (kind > BH_K_BOOL) return false;
+    if (kind <= BH_K_BYTES) {
+      uint32_t e2 = lp + b1;
+      if (e2 > end) { if (kind == BH_K_BYTES) return false; e2 = end; }
+      const uint32_t part = f >> 16;
+#pragma unroll
+      for (int k = 0; k < BH_MAX_KEY_PARTS; k++)
+        if (part == (uint32_t)k + 1) { P.ppos[k] = lp - r.off; P.plen[k] = e2 - lp; }
+      lp = e2;
+    } else {
+      uint32_t pos = lp - 1 - r.off;         // back to the byte after the tag
+      if (!decode_known_field(r, f, pos, len, P)) return false;
+      lp = r.off + pos;
+    }
+  }
+  return true;
+}
+
+__device__ __forceinline__ uint64_t hash_span_smem(const SmemRd& r, uint32_t lp, uint32_t n, uint32_t field, uint64_t h) {
+  uint32_t a = lp & ~3u;
+  const uint32_t sh = (lp & 3u) * 8u;
+  uint32_t w0 = r.w32(a);
+  a += 4;
+  uint32_t i = 0;
+#pragma unroll 1
+  for (; i + 8 <= n; i += 8) {
+    const uint32_t w1 = r.w32(a), w2 = r.w32(a + 4);
+    const uint32_t lo = __funnelshift_r(w0, w1, sh), hi = __funnelshift_r(w1, w2, sh);
+    h = absorb(h, ((uint64_t)hi << 32) | lo);
+    w0 = w2; a += 8;
+  }
+  if (i < n) {
+    const uint32_t rem = n - i;
+    const uint32_t w1 = r.w32(a), w2 = r.w32(a + 4);   // may read past the event: masked below, inside the buffer's slack
+    const uint32_t lo = __funnelshift_r(w0, w1, sh), hi = __funnelshift_r(w1, w2, sh);
+    const uint64_t w = ((uint64_t)hi << 32) | lo;
+    h = absorb(h, w & ((1ull << (8 * rem)) - 1));
+  }
+  return absorb(h, len_word(n, field));
+}
+
+__device__ __forceinline__ uint64_t event_key_hash_smem(const DevSchema& S, const SmemRd& r, const Parsed& P) {
+  if (S.status_part) return (uint64_t)P.status;
+  if (S.identity_key) return (uint64_t)P.pval[0];
+  uint64_t h = S.hash_seed ^ kHashInit;
+#pragma unroll
+  for (int k = 0; k < BH_MAX_KEY_PARTS; k++) {
+    if ((uint32_t)k >= S.n_parts) break;
+    if (S.part_is_len[k]) h = hash_span_smem(r, r.off + P.ppos[k], P.plen[k], S.part_field[k], h);
+    else h = absorb(h, varint_word(P.pval[k], S.part_field[k]));
+  }
+  return fmix64(h);
+}
+
+// drop rules after a successful decode.  Returns BH_EV_*.  `ival` is the value for integer value
+// kinds, `value` for the others.
+__device__ __forceinline__ uint32_t finish_event(const DevSchema& S, const Parsed& P, double& value, int32_t& ival, uint32_t& status) {
+  value = P.value; ival = (int32_t)P.uval; status = P.status;
   if (S.has_enum && !(P.status < 64 && ((S.enum_mask >> P.status) & 1ull))) return BH_EV_DROP_ENUM;
-  if ((S.ops & (BH_OP_SUM | BH_OP_MIN | BH_OP_MAX | BH_OP_HIST)) && P.value != P.value) return BH_EV_DROP_NAN;
+  if (!S.int_values && (S.ops & (BH_OP_SUM | BH_OP_MIN | BH_OP_MAX | BH_OP_HIST)) && P.value != P.value) return BH_EV_DROP_NAN;
   return BH_EV_OK;
+}
+
+__device__ __forceinline__ uint32_t decode_and_check_smem(const DevSchema& S, const SmemRd& r, uint32_t len, uint64_t& kh,
+                                                          double& value, int32_t& ival, uint32_t& status) {
+  Parsed P;
+  if (S.dbg & 1) { kh = r.off + len; value = 0.0; ival = (int32_t)len; status = 0; return BH_EV_OK; }
+  if (!decode_fast(S, r, len, P)) {
+    Parsed Q;   // a separate object: P must not escape into the out-of-line slow path (it would live in local memory)
+    if (!decode_event(S, r, len, Q)) { kh = 0; value = 0.0; ival = 0; status = 0; return BH_EV_DROP_DECODE; }
+    P = Q;
+  }
+  kh = (S.dbg & 2) ? (uint64_t)P.ppos[0] * 0x9E3779B97F4A7C15ull + P.status : event_key_hash_smem(S, r, P);
+  return finish_event(S, P, value, ival, status);
+}
+
+__device__ __noinline__ uint32_t decode_and_check_gmem(const DevSchema& S, const uint8_t* p, uint32_t len, uint64_t& kh,
+                                                       double& value, int32_t& ival, uint32_t& status) {
+  Parsed P;
+  GmemRd r{p};
+  if (!decode_event(S, r, len, P)) { kh = 0; value = 0.0; ival = 0; status = 0; return BH_EV_DROP_DECODE; }
+  kh = event_key_hash(S, r, P);
+  return finish_event(S, P, value, ival, status);
 }
 
 // =========================================================================================
 // raw path: stage a warp's batch of messages in shared memory, one lane per message
 // =========================================================================================
-constexpr uint32_t kWarpBuf = 2560;                 // payload bytes staged per warp batch
-constexpr uint32_t kWarpBufAlloc = kWarpBuf + 32;   // + alignment head + over-read slack
+constexpr uint32_t kWarpBuf = 2304;                                  // payload bytes staged per warp batch (32 x 72)
+constexpr uint32_t kWarpChunks = (kWarpBuf / 16 + 1 + 31) / 32;      // 16-byte chunks per lane (5)
+constexpr uint32_t kWarpBufAlloc = kWarpBuf + kWarpBuf / 16 + 64;    // + skew padding + over-read slack
 constexpr int kRawThreads = 768;
 
+// streaming 128-bit load; NOT volatile so that the loads of one batch are issued back to back
 __device__ __forceinline__ uint4 ldg_stream(const uint4* p) {
   uint4 v;
-  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+  asm("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
   return v;
 }
+__device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" :: "l"(p)); }
 
-// Handler interface shared by the fused and the decode-only kernel.
+// Handler interface shared by the fused and the decode-only kernel.  Each warp takes batches of 32
+// consecutive messages, copies their bytes (one contiguous range) into its shared buffer with
+// coalesced 128-bit loads, then every lane parses its own message.  The offsets of the NEXT batch are
+// loaded before the current one is parsed, and the lines the batch after that will touch are
+// prefetched into L2, so a warp rarely waits for HBM.
 template <class Sink>
 __device__ __forceinline__ void raw_warp_loop(const DevSchema& S, const uint8_t* __restrict__ payload,
                                               const uint32_t* __restrict__ offsets, uint32_t cs, uint32_t ce,
-                                              uint8_t* wbuf, Sink& sink) {
+                                              uint32_t wb, Sink& sink) {
   const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
   const uint32_t total16 = (offsets[ce] + 15u) & ~15u;   // readable bound of this chunk
-  for (uint32_t e0 = cs + warp * 32; e0 < ce; e0 += nwarps * 32) {
+  const uint32_t step = nwarps * 32;
+  uint32_t e0 = cs + warp * 32;
+  uint32_t n0 = 0, n1 = 0;                                // offsets of the batch about to be processed
+  if (e0 + lane < ce) { n0 = offsets[e0 + lane]; n1 = offsets[e0 + lane + 1]; }
+  for (; e0 < ce; e0 += step) {
     const uint32_t e = e0 + lane;
     const bool valid = e < ce;
-    uint32_t o0 = 0, o1 = 0;
-    if (valid) { o0 = offsets[e]; o1 = offsets[e + 1]; }
+    const uint32_t o0 = n0, o1 = n1;
+    {                                                     // next batch's offsets; lines of the one after
+      const uint32_t en = e + step;
+      n0 = 0; n1 = 0;
+      if (en < ce) { n0 = offsets[en]; n1 = offsets[en + 1]; }
+      const uint32_t e2 = e0 + 2 * step;
+      if (e2 < ce) {
+        if (lane == 0) prefetch_l2(offsets + e2);
+        sink.prefetch(e2, lane);
+        // payload two batches ahead: its byte range is not known yet; extrapolate from this batch's
+        const uint32_t first = __shfl_sync(0xFFFFFFFFu, o0, 0), last = __shfl_sync(0xFFFFFFFFu, o1, 31);
+        const uint32_t guess = first + 2u * (last - first) * nwarps + lane * 128u;
+        if (lane < 18 && guess >= first && guess < total16) prefetch_l2(payload + guess);
+      }
+    }
     const uint32_t cnt = min(32u, ce - e0);
     uint32_t done = 0;
     while (done < cnt) {
       const uint32_t b0 = __shfl_sync(0xFFFFFFFFu, o0, done);
       const uint32_t A = b0 & ~15u;
       const bool fits = valid && lane >= done && o1 >= o0 && o0 >= A && (o1 - A) <= kWarpBuf;
-      uint32_t mask = __ballot_sync(0xFFFFFFFFu, fits) >> done;
+      const uint32_t mask = __ballot_sync(0xFFFFFFFFu, fits) >> done;
       uint32_t m = mask == 0xFFFFFFFFu ? 32u : (uint32_t)__ffs(~mask) - 1u;   // leading run of lanes that fit
-      uint32_t outcome; uint64_t kh; double value; uint32_t status;
+      uint32_t outcome; uint64_t kh; double value; int32_t ival; uint32_t status;
       bool mine;
       if (m == 0) {                    // a single oversized (or inconsistent) message: parse from global
         m = 1;
         mine = lane == done;
         if (mine) {
-          if (o1 < o0) { outcome = BH_EV_DROP_DECODE; kh = 0; value = 0.0; status = 0; }
-          else { GmemRd r{payload + o0}; outcome = decode_and_check(S, r, o1 - o0, kh, value, status); }
+          if (o1 < o0) { outcome = BH_EV_DROP_DECODE; kh = 0; value = 0.0; ival = 0; status = 0; }
+          else outcome = decode_and_check_gmem(S, payload + o0, o1 - o0, kh, value, ival, status);
         }
       } else {
-        uint32_t bend = __shfl_sync(0xFFFFFFFFu, o1, done + m - 1);
-        uint32_t B = min((bend + 15u) & ~15u, total16);
+        const uint32_t bend = __shfl_sync(0xFFFFFFFFu, o1, done + m - 1);
+        const uint32_t B = min((bend + 15u) & ~15u, total16);
         const uint4* src = reinterpret_cast<const uint4*>(payload + A);
-        uint4* dst = reinterpret_cast<uint4*>(wbuf);
-        uint32_t nvec = (B - A) >> 4;
-        for (uint32_t i = lane; i < nvec; i += 32) dst[i] = ldg_stream(src + i);
+        const uint32_t nvec = (B - A) >> 4;
+        uint4 v[kWarpChunks];
+#pragma unroll
+        for (uint32_t k = 0; k < kWarpChunks; k++)
+          if (lane + 32 * k < nvec && !(S.dbg & 4)) v[k] = ldg_stream(src + lane + 32 * k);
+#pragma unroll
+        for (uint32_t k = 0; k < kWarpChunks; k++) {
+          const uint32_t i = lane + 32 * k;
+          if (i < nvec) {
+            const uint32_t d = wb + skew(i << 4);   // a 16-byte chunk never straddles a 64-byte block
+            sts32(d, v[k].x); sts32(d + 4, v[k].y); sts32(d + 8, v[k].z); sts32(d + 12, v[k].w);
+          }
+        }
         __syncwarp();
         mine = lane >= done && lane < done + m;
-        if (mine) { SmemRd r{wbuf + (o0 - A)}; outcome = decode_and_check(S, r, o1 - o0, kh, value, status); }
+        if (mine) { SmemRd r{wb, o0 - A}; outcome = decode_and_check_smem(S, r, o1 - o0, kh, value, ival, status); }
       }
-      if (mine) sink.event(e, outcome, kh, value, status);
+      if (mine) sink.event(e, outcome, kh, value, ival, status);
       __syncwarp();
       done += m;
     }
   }
 }
 
+template <bool INTV>
 struct AggSink {
   const DevSchema& S; const DevTables& T; const SmemTable& M;
   const uint64_t* ts; uint64_t wbase; LaneCounters& C;
-  __device__ __forceinline__ void event(uint32_t e, uint32_t outcome, uint64_t kh, double value, uint32_t) {
-    if (outcome != BH_EV_OK) { C.c[outcome]++; return; }
+  __device__ __forceinline__ void prefetch(uint32_t e2, uint32_t lane) const {
+    if (S.has_window && ts && lane < 2) prefetch_l2(ts + e2 + lane * 16);
+  }
+  __device__ __forceinline__ void event(uint32_t e, uint32_t outcome, uint64_t kh, double value, int32_t ival, uint32_t) {
+    if (outcome != BH_EV_OK) { C.bump(outcome); return; }
     uint64_t win = 0;
     if (S.has_window) win = div64(ts ? ts[e] : 0ull, S.wdiv);
-    aggregate_event(S, T, M, kh, win, wbase, value, C);
+    aggregate_event<INTV>(S, T, M, kh, win, wbase, value, ival, C);
   }
 };
 
+template <bool INTV>
 __global__ void __launch_bounds__(kRawThreads, 1)
 k_process_raw(const __grid_constant__ DevSchema S, const __grid_constant__ DevTables T,
               const uint8_t* __restrict__ payload, const uint32_t* __restrict__ offsets,
               const uint64_t* __restrict__ ts, uint32_t n, uint32_t chunk, uint32_t ns) {
   extern __shared__ __align__(16) uint8_t smem[];
   __shared__ uint32_t s_cnt[8];
-  SmemTable M = smem_table_carve(smem, ns);
-  uint8_t* wbuf = smem + (size_t)ns * kSmemSlotBytes + (size_t)(threadIdx.x >> 5) * kWarpBufAlloc;
-  smem_table_clear(M);
+  const bool hist = (S.ops & BH_OP_HIST) != 0;
+  const SmemTable M = smem_table_carve<INTV>(smem, ns, hist);
+  const uint32_t wb = (uint32_t)__cvta_generic_to_shared(smem) + ((ns * smem_slot_bytes(INTV, hist) + 15u) & ~15u) +
+                      (threadIdx.x >> 5) * kWarpBufAlloc;
+  smem_table_clear<INTV>(M);
   if (threadIdx.x < 8) s_cnt[threadIdx.x] = 0;
   __syncthreads();
   const uint32_t cs = min(n, blockIdx.x * chunk), ce = min(n, cs + chunk);
@@ -428,18 +698,22 @@ k_process_raw(const __grid_constant__ DevSchema S, const __grid_constant__ DevTa
   uint64_t wbase = 0;
   if (cs < ce) {
     if (S.has_window) { uint64_t w0 = div64(ts ? ts[cs] : 0ull, S.wdiv); wbase = w0 ? w0 - 1 : 0; }
-    AggSink sink{S, T, M, ts, wbase, C};
-    raw_warp_loop(S, payload, offsets, cs, ce, wbuf, sink);
+    AggSink<INTV> sink{S, T, M, ts, wbase, C};
+    raw_warp_loop(S, payload, offsets, cs, ce, wb, sink);
   }
   __syncthreads();
-  smem_table_flush(S, T, M, wbase);
+  smem_table_flush<INTV>(S, T, M, wbase);
   counters_flush(T, C, s_cnt);
 }
 
 struct ColumnSink {
+  const DevSchema& S;
   uint64_t* kh; double* val; int32_t* status; uint8_t* outcome;
-  __device__ __forceinline__ void event(uint32_t e, uint32_t oc, uint64_t k, double v, uint32_t st) {
-    kh[e] = k; val[e] = v; status[e] = (int32_t)st; outcome[e] = (uint8_t)oc;
+  __device__ __forceinline__ void prefetch(uint32_t, uint32_t) const {}
+  __device__ __forceinline__ void event(uint32_t e, uint32_t oc, uint64_t k, double v, int32_t iv, uint32_t st) {
+    // integer value kinds: the fast path leaves `v` unset; (double)(int32) is the JS number
+    const bool have = oc != BH_EV_DROP_DECODE;
+    kh[e] = k; val[e] = have && S.int_values ? (double)iv : v; status[e] = (int32_t)st; outcome[e] = (uint8_t)oc;
   }
 };
 
@@ -448,11 +722,11 @@ k_decode(const __grid_constant__ DevSchema S, const uint8_t* __restrict__ payloa
          const uint32_t* __restrict__ offsets, uint32_t n, uint32_t chunk, uint64_t* kh, double* val,
          int32_t* status, uint8_t* outcome) {
   extern __shared__ __align__(16) uint8_t smem[];
-  uint8_t* wbuf = smem + (size_t)(threadIdx.x >> 5) * kWarpBufAlloc;
+  const uint32_t wb = (uint32_t)__cvta_generic_to_shared(smem) + (threadIdx.x >> 5) * kWarpBufAlloc;
   const uint32_t cs = min(n, blockIdx.x * chunk), ce = min(n, cs + chunk);
   if (cs >= ce) return;
-  ColumnSink sink{kh, val, status, outcome};
-  raw_warp_loop(S, payload, offsets, cs, ce, wbuf, sink);
+  ColumnSink sink{S, kh, val, status, outcome};
+  raw_warp_loop(S, payload, offsets, cs, ce, wb, sink);
 }
 
 // =========================================================================================
@@ -466,8 +740,8 @@ k_process_columns(const __grid_constant__ DevSchema S, const __grid_constant__ D
                   const double* __restrict__ val, uint64_t n, uint64_t chunk, uint32_t ns) {
   extern __shared__ __align__(16) uint8_t smem[];
   __shared__ uint32_t s_cnt[8];
-  SmemTable M = smem_table_carve(smem, ns);
-  smem_table_clear(M);
+  const SmemTable M = smem_table_carve<false>(smem, ns, (S.ops & BH_OP_HIST) != 0);
+  smem_table_clear<false>(M);
   if (threadIdx.x < 8) s_cnt[threadIdx.x] = 0;
   __syncthreads();
   const uint64_t cs = min(n, (uint64_t)blockIdx.x * chunk), ce = min(n, cs + chunk);
@@ -476,14 +750,14 @@ k_process_columns(const __grid_constant__ DevSchema S, const __grid_constant__ D
   if (cs < ce && S.has_window) { uint64_t w0 = div64(ts[cs], S.wdiv); wbase = w0 ? w0 - 1 : 0; }
   const bool need_value = (S.ops & (BH_OP_SUM | BH_OP_MIN | BH_OP_MAX | BH_OP_HIST)) != 0;
   for (uint64_t i = cs + threadIdx.x; i < ce; i += blockDim.x) {
-    uint64_t k = kh[i];
-    double v = val ? val[i] : 0.0;
-    uint64_t win = S.has_window ? div64(ts[i], S.wdiv) : 0ull;
-    if (need_value && v != v) { C.c[C_NAN]++; continue; }
-    aggregate_event(S, T, M, k, win, wbase, v, C);
+    const uint64_t k = kh[i];
+    const double v = val ? val[i] : 0.0;
+    const uint64_t win = S.has_window ? div64(ts[i], S.wdiv) : 0ull;
+    if (need_value && v != v) { C.bump(C_NAN); continue; }
+    aggregate_event<false>(S, T, M, k, win, wbase, v, 0, C);
   }
   __syncthreads();
-  smem_table_flush(S, T, M, wbase);
+  smem_table_flush<false>(S, T, M, wbase);
   counters_flush(T, C, s_cnt);
 }
 
@@ -603,19 +877,19 @@ __global__ void k_close_release(const __grid_constant__ DevTables T, uint64_t wi
 // once per device, with that device current (bh_create)
 cudaError_t configure_kernels(const LaunchGeom& G) {
   int dyn = G.smem_optin - 1024;   // leave room for the kernels' static shared memory
-  cudaError_t e = cudaFuncSetAttribute(k_process_raw, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn);
+  cudaError_t e = cudaFuncSetAttribute(k_process_raw<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn);
+  if (e != cudaSuccess) return e;
+  e = cudaFuncSetAttribute(k_process_raw<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn);
   if (e != cudaSuccess) return e;
   e = cudaFuncSetAttribute(k_decode, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn);
   if (e != cudaSuccess) return e;
   return cudaFuncSetAttribute(k_process_columns, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn);
 }
 
-static uint32_t pick_smem_slots(const DevTables& T, const LaunchGeom& G, size_t other_bytes) {
-  // front table: as many slots as the window table has, capped by what fits beside the warp buffers
-  uint64_t want = T.cap < 64 ? 64 : T.cap;
-  uint32_t ns = 2048;
-  while ((uint64_t)ns > want) ns >>= 1;
-  while (ns > 64 && (size_t)ns * kSmemSlotBytes + other_bytes + 1024 > (size_t)G.smem_optin) ns >>= 1;
+static uint32_t pick_smem_slots(bool intv, bool hist, const LaunchGeom& G, size_t other_bytes) {
+  // front table: the largest power of two (<= 4096 slots) that fits beside the warp buffers
+  uint32_t ns = 4096;
+  while (ns > 64 && (size_t)ns * smem_slot_bytes(intv, hist) + 16 + other_bytes + 1024 > (size_t)G.smem_optin) ns >>= 1;
   return ns;
 }
 
@@ -623,16 +897,17 @@ cudaError_t launch_process_raw(const DevSchema& S, const DevTables& T, const Lau
                                const uint8_t* payload, const uint32_t* offsets, const uint64_t* ts,
                                uint32_t n, cudaStream_t st, int* launches) {
   if (n == 0) return cudaSuccess;
+  const bool hist = (S.ops & BH_OP_HIST) != 0, intv = S.int_values != 0;
   size_t wbytes = (size_t)(kRawThreads / 32) * kWarpBufAlloc;
-  uint32_t ns = pick_smem_slots(T, G, wbytes);
-  size_t smem = (size_t)ns * kSmemSlotBytes + wbytes;
-  uint32_t per = kRawThreads;  // events per CTA pass
+  uint32_t ns = pick_smem_slots(intv, hist, G, wbytes);
+  size_t smem = (((size_t)ns * smem_slot_bytes(intv, hist) + 15) & ~(size_t)15) + wbytes;
   uint32_t grid = (uint32_t)G.sms;
-  uint32_t need = (n + per - 1) / per;
+  uint32_t need = (n + kRawThreads - 1) / kRawThreads;
   if (need < grid) grid = need;
   uint32_t chunk = (n + grid - 1) / grid;
   chunk = (chunk + 31u) & ~31u;
-  k_process_raw<<<grid, kRawThreads, smem, st>>>(S, T, payload, offsets, ts, n, chunk, ns);
+  if (intv) k_process_raw<true><<<grid, kRawThreads, smem, st>>>(S, T, payload, offsets, ts, n, chunk, ns);
+  else k_process_raw<false><<<grid, kRawThreads, smem, st>>>(S, T, payload, offsets, ts, n, chunk, ns);
   if (launches) (*launches)++;
   return cudaGetLastError();
 }
@@ -655,8 +930,9 @@ cudaError_t launch_process_columns(const DevSchema& S, const DevTables& T, const
                                    const uint64_t* kh, const uint64_t* ts, const double* val,
                                    uint64_t n, cudaStream_t st, int* launches) {
   if (n == 0) return cudaSuccess;
-  uint32_t ns = pick_smem_slots(T, G, 0);
-  size_t smem = (size_t)ns * kSmemSlotBytes;
+  const bool hist = (S.ops & BH_OP_HIST) != 0;
+  uint32_t ns = pick_smem_slots(false, hist, G, 0);
+  size_t smem = (size_t)ns * smem_slot_bytes(false, hist) + 16;
   uint64_t grid = (uint64_t)G.sms;
   uint64_t need = (n + kColThreads - 1) / kColThreads;
   if (need < grid) grid = need;
