@@ -576,7 +576,8 @@ __device__ __noinline__ uint32_t decode_and_check_gmem(const DevSchema& S, const
 constexpr uint32_t kWarpBuf = 2304;                                  // payload bytes staged per warp batch (32 x 72)
 constexpr uint32_t kWarpChunks = (kWarpBuf / 16 + 1 + 31) / 32;      // 16-byte chunks per lane (5)
 constexpr uint32_t kWarpBufAlloc = kWarpBuf + kWarpBuf / 16 + 64;    // + skew padding + over-read slack
-constexpr int kRawThreads = 768;
+constexpr int kRawThreads = 1024;      // decode-only kernel and the integer-table fused kernel
+constexpr int kRawThreadsF64 = 768;    // fused kernel with the (larger) f64 table: fewer warp buffers, 4096 slots still fit
 
 // streaming 128-bit load; NOT volatile so that the loads of one batch are issued back to back
 __device__ __forceinline__ uint4 ldg_stream(const uint4* p) {
@@ -680,7 +681,7 @@ struct AggSink {
 };
 
 template <bool INTV>
-__global__ void __launch_bounds__(kRawThreads, 1)
+__global__ void __launch_bounds__(INTV ? kRawThreads : kRawThreadsF64, 1)
 k_process_raw(const __grid_constant__ DevSchema S, const __grid_constant__ DevTables T,
               const uint8_t* __restrict__ payload, const uint32_t* __restrict__ offsets,
               const uint64_t* __restrict__ ts, uint32_t n, uint32_t chunk, uint32_t ns) {
@@ -898,16 +899,17 @@ cudaError_t launch_process_raw(const DevSchema& S, const DevTables& T, const Lau
                                uint32_t n, cudaStream_t st, int* launches) {
   if (n == 0) return cudaSuccess;
   const bool hist = (S.ops & BH_OP_HIST) != 0, intv = S.int_values != 0;
-  size_t wbytes = (size_t)(kRawThreads / 32) * kWarpBufAlloc;
+  const uint32_t threads = intv ? kRawThreads : kRawThreadsF64;
+  size_t wbytes = (size_t)(threads / 32) * kWarpBufAlloc;
   uint32_t ns = pick_smem_slots(intv, hist, G, wbytes);
   size_t smem = (((size_t)ns * smem_slot_bytes(intv, hist) + 15) & ~(size_t)15) + wbytes;
   uint32_t grid = (uint32_t)G.sms;
-  uint32_t need = (n + kRawThreads - 1) / kRawThreads;
+  uint32_t need = (n + threads - 1) / threads;
   if (need < grid) grid = need;
   uint32_t chunk = (n + grid - 1) / grid;
   chunk = (chunk + 31u) & ~31u;
   if (intv) k_process_raw<true><<<grid, kRawThreads, smem, st>>>(S, T, payload, offsets, ts, n, chunk, ns);
-  else k_process_raw<false><<<grid, kRawThreads, smem, st>>>(S, T, payload, offsets, ts, n, chunk, ns);
+  else k_process_raw<false><<<grid, kRawThreadsF64, smem, st>>>(S, T, payload, offsets, ts, n, chunk, ns);
   if (launches) (*launches)++;
   return cudaGetLastError();
 }
