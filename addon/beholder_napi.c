@@ -1,0 +1,129 @@
+/*
+ * beholder_napi.c — N-API shim over libbeholder_gpu.so (include/beholder_gpu.h).
+ *
+ * SOURCE ONLY: node, node-gyp and node_api.h are not present in the image this repository is built
+ * and tested in, so this file has never been compiled there.  It uses only the stable N-API C ABI
+ * and the C-ABI of the library, which IS tested (Python ctypes + GPU tests).  Build on a box with
+ * Node >= 12:   node-gyp rebuild   (binding.gyp next to this file).
+ *
+ * JS surface (wrapped by beholder-gpu.js):
+ *   const ctx = native.create(configBuffer)        // bh_create; configBuffer = a packed bh_config
+ *   native.push(ctx, buffer, tsMs)                 // bh_push: rmsg.message.content (index.js:129)
+ *   native.flush(ctx)      -> committedSeq         // bh_flush
+ *   native.poll(ctx)       -> committedSeq         // bh_poll_committed (non-blocking)
+ *   native.snapshot(ctx, windowId, cap) -> Buffer  // bh_snapshot: packed bh_record rows
+ *   native.counters(ctx)   -> Buffer               // bh_get_counters
+ *   native.destroy(ctx)
+ */
+#include <node_api.h>
+#include <stdint.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include "../include/beholder_gpu.h"
+
+#define NAPI_OK(call) do { if ((call) != napi_ok) { napi_throw_error(env, NULL, #call " failed"); return NULL; } } while (0)
+
+static bh_ctx* unwrap(napi_env env, napi_value v) {
+  void* p = NULL;
+  if (napi_get_value_external(env, v, &p) != napi_ok) return NULL;
+  return (bh_ctx*)p;
+}
+
+static void finalize_ctx(napi_env env, void* data, void* hint) { (void)env; (void)hint; bh_destroy((bh_ctx*)data); }
+
+static napi_value throw_bh(napi_env env, bh_ctx* ctx, int rc) {
+  char code[16]; snprintf(code, sizeof code, "%d", rc);
+  napi_throw_error(env, code, bh_last_error(ctx));
+  return NULL;
+}
+
+static napi_value Create(napi_env env, napi_callback_info info) {
+  size_t argc = 1; napi_value argv[1]; void* data; size_t len;
+  NAPI_OK(napi_get_cb_info(env, info, &argc, argv, NULL, NULL));
+  NAPI_OK(napi_get_buffer_info(env, argv[0], &data, &len));
+  if (len != sizeof(bh_config)) { napi_throw_error(env, NULL, "config buffer must be sizeof(bh_config) bytes"); return NULL; }
+  bh_config cfg; memcpy(&cfg, data, sizeof cfg);
+  bh_ctx* ctx = NULL;
+  int rc = bh_create(&cfg, &ctx);
+  if (rc != BH_OK) return throw_bh(env, NULL, rc);       /* no device -> BH_ERR_NO_DEVICE: there is no CPU path */
+  napi_value ext;
+  NAPI_OK(napi_create_external(env, ctx, finalize_ctx, NULL, &ext));
+  return ext;
+}
+
+static napi_value Push(napi_env env, napi_callback_info info) {
+  size_t argc = 3; napi_value argv[3]; void* data; size_t len; int64_t ts = 0;
+  NAPI_OK(napi_get_cb_info(env, info, &argc, argv, NULL, NULL));
+  bh_ctx* ctx = unwrap(env, argv[0]);
+  NAPI_OK(napi_get_buffer_info(env, argv[1], &data, &len));
+  if (argc > 2) napi_get_value_int64(env, argv[2], &ts);
+  int rc = bh_push(ctx, (const uint8_t*)data, (uint32_t)len, (uint64_t)ts);   /* copied into the pinned ring */
+  if (rc != BH_OK) return throw_bh(env, ctx, rc);
+  return NULL;
+}
+
+static napi_value seq_result(napi_env env, uint64_t seq) {
+  napi_value v; NAPI_OK(napi_create_bigint_uint64(env, seq, &v)); return v;
+}
+
+static napi_value Flush(napi_env env, napi_callback_info info) {
+  size_t argc = 1; napi_value argv[1]; uint64_t seq = 0;
+  NAPI_OK(napi_get_cb_info(env, info, &argc, argv, NULL, NULL));
+  bh_ctx* ctx = unwrap(env, argv[0]);
+  int rc = bh_flush(ctx, &seq);
+  if (rc != BH_OK) return throw_bh(env, ctx, rc);
+  return seq_result(env, seq);
+}
+
+static napi_value Poll(napi_env env, napi_callback_info info) {
+  size_t argc = 1; napi_value argv[1]; uint64_t seq = 0;
+  NAPI_OK(napi_get_cb_info(env, info, &argc, argv, NULL, NULL));
+  bh_ctx* ctx = unwrap(env, argv[0]);
+  int rc = bh_poll_committed(ctx, &seq);
+  if (rc != BH_OK) return throw_bh(env, ctx, rc);
+  return seq_result(env, seq);
+}
+
+static napi_value Snapshot(napi_env env, napi_callback_info info) {
+  size_t argc = 3; napi_value argv[3]; bool lossless; uint64_t window = 0; uint32_t cap = 4096;
+  NAPI_OK(napi_get_cb_info(env, info, &argc, argv, NULL, NULL));
+  bh_ctx* ctx = unwrap(env, argv[0]);
+  if (argc > 1) napi_get_value_bigint_uint64(env, argv[1], &window, &lossless);
+  if (argc > 2) napi_get_value_uint32(env, argv[2], &cap);
+  void* out; napi_value buf; uint64_t n = 0;
+  NAPI_OK(napi_create_buffer(env, (size_t)cap * sizeof(bh_record), &out, &buf));
+  int rc = bh_snapshot(ctx, window, (bh_record*)out, cap, &n);
+  if (rc != BH_OK) return throw_bh(env, ctx, rc);
+  napi_value res, nv;
+  NAPI_OK(napi_create_object(env, &res));
+  NAPI_OK(napi_create_bigint_uint64(env, n, &nv));
+  NAPI_OK(napi_set_named_property(env, res, "rows", nv));
+  NAPI_OK(napi_set_named_property(env, res, "data", buf));
+  return res;
+}
+
+static napi_value Counters(napi_env env, napi_callback_info info) {
+  size_t argc = 1; napi_value argv[1];
+  NAPI_OK(napi_get_cb_info(env, info, &argc, argv, NULL, NULL));
+  bh_ctx* ctx = unwrap(env, argv[0]);
+  void* out; napi_value buf;
+  NAPI_OK(napi_create_buffer(env, sizeof(bh_counters), &out, &buf));
+  int rc = bh_get_counters(ctx, (bh_counters*)out);
+  if (rc != BH_OK && rc != BH_ERR_TABLE_FULL && rc != BH_ERR_WINDOW_RING) return throw_bh(env, ctx, rc);
+  return buf;
+}
+
+static napi_value Init(napi_env env, napi_value exports) {
+  napi_property_descriptor props[] = {
+    {"create", NULL, Create, NULL, NULL, NULL, napi_default, NULL},
+    {"push", NULL, Push, NULL, NULL, NULL, napi_default, NULL},
+    {"flush", NULL, Flush, NULL, NULL, NULL, napi_default, NULL},
+    {"poll", NULL, Poll, NULL, NULL, NULL, napi_default, NULL},
+    {"snapshot", NULL, Snapshot, NULL, NULL, NULL, napi_default, NULL},
+    {"counters", NULL, Counters, NULL, NULL, NULL, napi_default, NULL},
+  };
+  napi_define_properties(env, exports, sizeof props / sizeof props[0], props);
+  return exports;
+}
+NAPI_MODULE(NODE_GYP_MODULE_NAME, Init)
