@@ -15,6 +15,7 @@ BH_MAX_FIELDS = 16
 BH_MAX_ENUM = 64
 BH_HIST_MAX = 64
 BH_ALL_WINDOWS = 0xFFFFFFFFFFFFFFFF
+BH_STATIC_EXPORT_MAX_OWNERS = 1024
 
 # bh_status
 BH_OK = 0
@@ -100,6 +101,7 @@ PROTOTYPES = {
     "bh_process_columns_device": (C.c_int, [C.c_void_p, _u64p, _u64p, _f64p, C.c_uint64, C.c_void_p]),
     "bh_decode_device": (C.c_int, [C.c_void_p, _u8p, _u32p, C.c_uint32, _u64p, _f64p, _i32p, _u8p, C.c_void_p]),
     "bh_export_window_device": (C.c_int, [C.c_void_p, C.c_uint64, C.c_uint32, C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint64, _u64p, C.c_void_p]),
+    "bh_export_window_static": (C.c_int, [C.c_void_p, C.c_uint64, C.c_uint32, C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint64, _u64p, C.c_void_p]),
     "bh_reset_device": (C.c_int, [C.c_void_p, C.c_void_p]),
     "bh_merge_records_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p]),
     "bh_sync": (C.c_int, [C.c_void_p]),

@@ -612,6 +612,22 @@ int bh_export_window_device(bh_ctx* c, uint64_t window_id, uint32_t n_owners, bh
   return BH_OK;
 }
 
+int bh_export_window_static(bh_ctx* c, uint64_t window_id, uint32_t n_owners, bh_record* d_records,
+                            uint32_t* d_hist, uint64_t cap, uint64_t owner_stride, uint64_t* d_owner_counts,
+                            void* stream) {
+  if (!c || !d_records || !d_owner_counts) return fail(c, BH_ERR_INVALID, "null argument");
+  if (n_owners > BH_STATIC_EXPORT_MAX_OWNERS)
+    return fail(c, BH_ERR_TOO_LARGE, "bh_export_window_static: n_owners %u exceeds the built-in scratch of %d owners; "
+                "use bh_export_window_device", n_owners, BH_STATIC_EXPORT_MAX_OWNERS);
+  if (!is_pow2(n_owners)) return fail(c, BH_ERR_INVALID, "n_owners must be a power of two");
+  if (owner_stride && owner_stride * n_owners > cap) return fail(c, BH_ERR_INVALID, "owner_stride * n_owners exceeds cap");
+  DeviceGuard guard(c->device);
+  cudaStream_t st = stream ? (cudaStream_t)stream : c->st_compute;
+  CU(c, launch_export_static(c->S, c->T, window_id, n_owners, d_records, d_hist, cap, owner_stride,
+                             (unsigned long long*)d_owner_counts, st));
+  return BH_OK;
+}
+
 int bh_reset_device(bh_ctx* c, void* stream) {
   if (!c) return BH_ERR_INVALID;
   DeviceGuard guard(c->device);

@@ -966,6 +966,34 @@ cudaError_t launch_export(const DevSchema& S, const DevTables& T, uint64_t windo
   return cudaGetLastError();
 }
 
+// ---- allocation-free export --------------------------------------------------------------------
+// Same kernels as launch_export, but the per-owner write cursors (the only scratch the export needs)
+// live in this file-scope device array instead of memory obtained from cudaMalloc.  Each GPU that loads
+// the library holds these 8 KB until the process exits.  In host code the NAME below is only a handle
+// for the runtime, not a device address: the address is looked up once per device with
+// cudaGetSymbolAddress (with that device current) and it is that pointer the kernels receive.
+static __device__ __align__(256) unsigned long long g_static_export_cursor[BH_STATIC_EXPORT_MAX_OWNERS];
+static unsigned long long* g_static_export_cursor_addr[64];   // per device ordinal, filled on first use
+
+cudaError_t launch_export_static(const DevSchema& S, const DevTables& T, uint64_t window_id, uint32_t n_owners,
+                                 bh_record* out, uint32_t* hist_out, uint64_t cap, uint64_t owner_stride,
+                                 unsigned long long* owner_counts, cudaStream_t st) {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  if (dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
+  if (!g_static_export_cursor_addr[dev]) {          // set-up: first call on this device
+    void* p = nullptr;
+    e = cudaGetSymbolAddress(&p, g_static_export_cursor);
+    if (e != cudaSuccess) return e;
+    g_static_export_cursor_addr[dev] = (unsigned long long*)p;
+  }
+  // k_export_prefix rewrites cursor[0 .. n_owners) on every call, so nothing of the previous call's
+  // contents is read; owner_counts is zeroed by launch_export (a memset, not an allocation).
+  return launch_export(S, T, window_id, n_owners, out, hist_out, cap, owner_stride, owner_counts,
+                       g_static_export_cursor_addr[dev], st);
+}
+
 cudaError_t launch_merge(const DevSchema& S, const DevTables& T, const bh_record* recs,
                          const uint32_t* hist, uint64_t n, cudaStream_t st) {
   if (n == 0) return cudaSuccess;

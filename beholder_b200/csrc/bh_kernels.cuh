@@ -26,6 +26,9 @@ cudaError_t launch_export(const DevSchema& S, const DevTables& T, uint64_t windo
                           bh_record* out, uint32_t* hist_out, uint64_t cap, uint64_t owner_stride,
                           unsigned long long* owner_counts, unsigned long long* owner_cursor,
                           cudaStream_t st);
+cudaError_t launch_export_static(const DevSchema& S, const DevTables& T, uint64_t window_id, uint32_t n_owners,
+                                 bh_record* out, uint32_t* hist_out, uint64_t cap, uint64_t owner_stride,
+                                 unsigned long long* owner_counts, cudaStream_t st);
 cudaError_t launch_merge(const DevSchema& S, const DevTables& T, const bh_record* recs,
                          const uint32_t* hist, uint64_t n, cudaStream_t st);
 cudaError_t launch_close_window(const DevTables& T, uint64_t window_id, cudaStream_t st);

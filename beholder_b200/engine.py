@@ -135,6 +135,13 @@ class Aggregator:
         self._ck(L.lib.bh_export_window_device(self._ctx, window_id, n_owners, _ptr(d_records), _ptr(d_hist), cap,
                                                owner_stride, _ptr(d_owner_counts), stream or None))
 
+    def export_window_static(self, window_id: int, n_owners: int, d_records, d_hist, cap: int, d_owner_counts,
+                             owner_stride: int = 0, stream: int = 0) -> None:
+        """export_window_device without any device allocation: the per-owner cursors sit in an 8 KB array
+        built into the library (at most BH_STATIC_EXPORT_MAX_OWNERS owners; calls on one GPU must not overlap)"""
+        self._ck(L.lib.bh_export_window_static(self._ctx, window_id, n_owners, _ptr(d_records), _ptr(d_hist), cap,
+                                               owner_stride, _ptr(d_owner_counts), stream or None))
+
     def reset_device(self, stream: int = 0) -> None:
         self._ck(L.lib.bh_reset_device(self._ctx, stream or None))
 

@@ -161,6 +161,25 @@ int bh_decode_device(bh_ctx* ctx, const uint8_t* d_payload, const uint32_t* d_of
 int bh_export_window_device(bh_ctx* ctx, uint64_t window_id, uint32_t n_owners, bh_record* d_records,
                             uint32_t* d_hist, uint64_t cap, uint64_t owner_stride,
                             uint64_t* d_owner_counts, void* stream);
+/* bh_export_window_device for callers that must not allocate device memory.  It has no counterpart in
+ * the reference.  Who needs it: a host that fixes its GPU memory budget at start-up and forbids the
+ * driver allocator afterwards (a serving process sharing the GPU under a hard memory cap, a real-time
+ * loop where cudaMalloc's implicit device synchronisation is unacceptable), or a caller that is inside
+ * a phase where the allocator may not be entered at all.  Arguments, output layout and results are
+ * those of bh_export_window_device; the difference is where the scratch (one write cursor per owner)
+ * lives: in an array built into the library image, BH_STATIC_EXPORT_MAX_OWNERS * 8 bytes = 8 KB that
+ * every GPU which loads the library keeps until the process exits.  The call allocates nothing: no
+ * cudaMalloc / cudaFree, no allocating library routine.
+ *   - n_owners above BH_STATIC_EXPORT_MAX_OWNERS is refused with BH_ERR_TOO_LARGE.
+ *   - The first call on a device looks up the array's device address (cudaGetSymbolAddress); make that
+ *     first call before starting any stream capture on that device.
+ *   - All calls on one GPU share the one array.  Each call rewrites the cursors it uses before reading
+ *     them, so earlier contents never leak in, but two calls that overlap on the GPU (different streams
+ *     or contexts) race on it: keep them ordered. */
+#define BH_STATIC_EXPORT_MAX_OWNERS 1024
+int bh_export_window_static(bh_ctx* ctx, uint64_t window_id, uint32_t n_owners, bh_record* d_records,
+                            uint32_t* d_hist, uint64_t cap, uint64_t owner_stride,
+                            uint64_t* d_owner_counts, void* stream);
 /* drop every window and zero the drop counters (the counters of index.js:32 "reset on restart") */
 int bh_reset_device(bh_ctx* ctx, void* stream);
 /* merge partial rows (from other GPUs) into this context's tables */
