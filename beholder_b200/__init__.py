@@ -11,7 +11,8 @@ from ._lib import (BeholderError, MODE_REFERENCE, MODE_WINDOWED, OP_COUNT, OP_SU
                    EV_OK, EV_DROP_DECODE, EV_DROP_ENUM, EV_DROP_NAN)
 from .engine import Aggregator, PinnedBuffer, RECORD_DTYPE
 from .handler import BeholderGPU, StubAMQP, StubRmsg
-from .schema import Schema, Field, telemetry_progress, encode
+from .schema import Schema, Field, telemetry_progress, telemetry_status, encode
+from . import metrics
 from .synth import SynthSpec, zipf_cdf
 
 __all__ = [

@@ -96,6 +96,7 @@ PROTOTYPES = {
     "bh_snapshot_hist": (C.c_int, [C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64)]),
     "bh_list_windows": (C.c_int, [C.c_void_p, _u64p, C.c_uint32, C.POINTER(C.c_uint32)]),
     "bh_close_window": (C.c_int, [C.c_void_p, C.c_uint64]),
+    "bh_restore": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64]),
     "bh_get_counters": (C.c_int, [C.c_void_p, C.POINTER(BhCounters)]),
     "bh_process_device": (C.c_int, [C.c_void_p, _u8p, _u32p, _u64p, C.c_uint32, C.c_void_p]),
     "bh_process_columns_device": (C.c_int, [C.c_void_p, _u64p, _u64p, _f64p, C.c_uint64, C.c_void_p]),

@@ -466,6 +466,29 @@ int bh_poll_committed(bh_ctx* c, uint64_t* seq) {
   return BH_OK;
 }
 
+static int ensure_export(bh_ctx* c, uint64_t cap, bool hist);
+
+// host-pointer merge: the restore side of bh_snapshot_hist
+int bh_restore(bh_ctx* c, const bh_record* recs, const uint32_t* hist, uint64_t n) {
+  if (!c || (n && !recs)) return fail(c, BH_ERR_INVALID, "null argument");
+  DeviceGuard guard(c->device);
+  int rc = submit_current(c);
+  if (rc) return rc;
+  const uint64_t chunk = 1u << 16;
+  bool with_hist = hist != nullptr && c->T.hist != nullptr;
+  rc = ensure_export(c, std::min<uint64_t>(std::max<uint64_t>(n, 1), chunk), with_hist);
+  if (rc) return rc;
+  for (uint64_t i = 0; i < n; i += c->export_cap) {
+    uint64_t m = std::min<uint64_t>(c->export_cap, n - i);
+    CU(c, cudaMemcpyAsync(c->d_export, recs + i, m * sizeof(bh_record), cudaMemcpyHostToDevice, c->st_compute));
+    if (with_hist) CU(c, cudaMemcpyAsync(c->d_export_hist, hist + i * c->T.hist_buckets, m * c->T.hist_buckets * 4, cudaMemcpyHostToDevice, c->st_compute));
+    CU(c, launch_merge(c->S, c->T, c->d_export, with_hist ? c->d_export_hist : nullptr, m, c->st_compute));
+    CU(c, cudaStreamSynchronize(c->st_compute));   // the caller's buffers are pageable: finish before the next chunk
+  }
+  bh_counters k;
+  return bh_get_counters(c, &k);
+}
+
 int bh_sync(bh_ctx* c) {
   if (!c) return BH_ERR_INVALID;
   DeviceGuard guard(c->device);

@@ -118,16 +118,15 @@ __device__ __forceinline__ void smem_table_clear(const SmemTable& M) {
 // plain store and readers that match the key wait for it (0xFF = not written yet).  No fence is needed:
 // only the one location is polled.  With histograms on, the HBM slot must be visible before the window
 // byte, which costs a block-level fence on that (rare) path only.
-__device__ uint32_t g_dbg_probes;
-__device__ __forceinline__ int smem_find_or_insert(const SmemTable& M, const DevTables& T, uint64_t kh,
-                                                   uint32_t wrel, uint64_t win, uint32_t* probes = nullptr) {
-  uint32_t x = (uint32_t)kh ^ (uint32_t)(kh >> 32) ^ (wrel * 0x85EBCA6Bu);
-  uint32_t slot = (x * 0x9E3779B1u) >> M.shift;
+// Slow half: claim a slot (or find the key someone else is inserting right now), starting at `slot`.
+// Kept out of line: the CAS and the wait loop make the compiler add yields and convergence barriers
+// that must not sit in the hot look-up loop.
+__device__ __noinline__ int smem_insert(const SmemTable& M, const DevTables& T, uint64_t kh, uint32_t wrel,
+                                        uint64_t win, uint32_t slot, int probes_left) {
   volatile unsigned long long* vkey = M.key;
   volatile uint8_t* vwrel = M.wrel;
 #pragma unroll 1
-  for (int p = 0; p < kSmemProbes; p++) {
-    if (probes) (*probes)++;
+  for (int p = 0; p < probes_left; p++) {
     unsigned long long k = vkey[slot];
     if (k == kEmptyKey) {
       k = atomicCAS(&M.key[slot], (unsigned long long)kEmptyKey, (unsigned long long)kh);
@@ -145,6 +144,24 @@ __device__ __forceinline__ int smem_find_or_insert(const SmemTable& M, const Dev
     slot = (slot + 1) & (M.ns - 1);
   }
   return -1;
+}
+
+// Hot half: read-only look-up (plain shared loads, no atomics, no waiting).
+__device__ __forceinline__ int smem_find_or_insert(const SmemTable& M, const DevTables& T, uint64_t kh,
+                                                   uint32_t wrel, uint64_t win) {
+  uint32_t x = (uint32_t)kh ^ (uint32_t)(kh >> 32) ^ (wrel * 0x85EBCA6Bu);
+  uint32_t slot = (x * 0x9E3779B1u) >> M.shift;
+  int p = 0;
+#pragma unroll 1
+  for (; p < kSmemProbes; p++) {
+    const unsigned long long k = M.key[slot];
+    const uint32_t w = M.wrel[slot];
+    if (k == kh && w == wrel) return (int)slot;
+    if (k == kEmptyKey || (k == kh && w == kWrelUnset)) break;   // not here (yet): go and insert / wait
+    slot = (slot + 1) & (M.ns - 1);
+  }
+  if (p == kSmemProbes) return -1;
+  return smem_insert(M, T, kh, wrel, win, slot, kSmemProbes - p);
 }
 
 struct LaneCounters {
@@ -169,7 +186,6 @@ __device__ __forceinline__ void aggregate_event(const DevSchema& S, const DevTab
   const uint64_t wr = win - wbase;
   int slot = -1;
   if (S.dbg & 16) slot = (int)((((uint32_t)kh ^ (uint32_t)(kh >> 32)) * 0x9E3779B1u) >> M.shift);
-  else if (S.dbg & 32) { uint32_t pr = 0; slot = smem_find_or_insert(M, T, kh, (uint32_t)wr, win, &pr); C.c[C_SPILL] += pr; }
   else if (kh < kLockKey && wr < 255ull) slot = smem_find_or_insert(M, T, kh, (uint32_t)wr, win);
   if (S.dbg & 8) { C.c[C_OK] += (slot >= 0); return; }
   if (slot >= 0) {

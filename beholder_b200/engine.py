@@ -181,6 +181,27 @@ class Aggregator:
             return (empty, np.zeros((0, self.hist_buckets), np.uint32)) if with_hist else empty
         return (np.concatenate(recs), np.concatenate(hists)) if with_hist else np.concatenate(recs)
 
+    # ---- snapshot / restore (the reference loses its counters on restart, index.js:32) ----
+    def restore(self, records: np.ndarray, hist: Optional[np.ndarray] = None) -> None:
+        records = np.ascontiguousarray(records, dtype=RECORD_DTYPE)
+        if hist is not None:
+            hist = np.ascontiguousarray(hist, dtype=np.uint32)
+        self._ck(L.lib.bh_restore(self._ctx, records.ctypes.data, hist.ctypes.data if hist is not None else None, len(records)))
+
+    def save(self, path: str) -> int:
+        """every open window (rows + histograms if kept) into an .npz file; returns the row count"""
+        with_hist = bool(self.ops & L.OP_HIST)
+        snap = self.snapshot_all(with_hist=with_hist)
+        recs, hist = snap if with_hist else (snap, np.zeros((0, self.hist_buckets), np.uint32))
+        np.savez_compressed(path, records=recs, hist=hist, counters=np.array(list(self.counters(check=False).values()), dtype=np.uint64))
+        return len(recs)
+
+    def load(self, path: str) -> int:
+        z = np.load(path)
+        recs = z["records"].view(RECORD_DTYPE) if z["records"].dtype != RECORD_DTYPE else z["records"]
+        self.restore(recs, z["hist"] if len(z["hist"]) else None)
+        return len(recs)
+
     def list_windows(self):
         out = np.zeros(1024, dtype=np.uint64)
         n = C.c_uint32()

@@ -27,7 +27,7 @@ from typing import Awaitable, Callable, Deque, Dict, List, Optional, Tuple
 
 from . import _lib as L
 from .engine import Aggregator
-from .schema import Schema, telemetry_progress
+from .schema import Schema, telemetry_progress, telemetry_status
 
 COUNTER_NAME = "beholder_progress_updates_total"                                       # index.js:31
 COUNTER_HELP = "Total number of messages processed in this processes lifetime"         # index.js:32
@@ -37,15 +37,16 @@ class GpuCounter:
     """prom-client Counter look-alike whose values live in the GPU table (index.js:30-34)."""
 
     def __init__(self, owner: "BeholderGPU", name: str = COUNTER_NAME, help: str = COUNTER_HELP,
-                 label_names=("status",)):
+                 label_names=("status",), counts=None):
         self._owner = owner
+        self._counts = counts or owner.status_counts
         self.name = name
         self.help = help
         self.labelNames = list(label_names)
 
     def get(self) -> dict:
         """same shape as prom-client 11.x Counter.get()"""
-        counts = self._owner.status_counts()
+        counts = self._counts()
         return {
             "help": self.help, "name": self.name, "type": "counter", "aggregator": "sum",
             "values": [{"value": v, "labels": {"status": k}} for k, v in counts.items()],
@@ -58,7 +59,7 @@ class GpuCounter:
     def metrics(self) -> str:
         """prom-client registry.metrics() text for this counter"""
         lines = [f"# HELP {self.name} {self.help}", f"# TYPE {self.name} counter"]
-        for k, v in self._owner.status_counts().items():
+        for k, v in self._counts().items():
             lines.append(f'{self.name}{{status="{k}"}} {v}')
         return "\n".join(lines) + "\n"
 
@@ -89,6 +90,7 @@ class BeholderGPU:
         self._pending: Deque[Tuple[int, object]] = collections.deque()   # (sequence number, rmsg)
         self._seq = 0
         self.progress_updates_total = GpuCounter(self)
+        self.status_agg = None
         self.trello_comments_total = HostCounter("beholder_trello_comments",
                                                  "Total trello comments crreated in this processes lifetime")
 
@@ -114,6 +116,39 @@ class BeholderGPU:
             else:
                 self._ack_upto(self.agg.poll_committed())
         return on_progress
+
+    # -- v1.telemetry.status (index.js:62-125): per-status counting of the sibling stream.
+    # The reference does NOT count this stream; `beholder_status_updates_total` is an added series.  Its
+    # I/O (db.updateStatus, Trello move, Telegram, Emby) stays on the host in `side_effects`; as in the
+    # reference that code is outside any try/catch (index.js:63-68), so an exception propagates and the
+    # message is not acked.  Unlike the reference, a message whose payload cannot be decoded is counted as
+    # dropped and acked instead of being redelivered forever.
+    def status_handler(self, side_effects: Optional[Callable[[object], Optional[Awaitable]]] = None,
+                       schema: Optional[Schema] = None):
+        if self.status_agg is None:
+            self.status_schema = schema or telemetry_status()
+            self.status_agg = Aggregator(self.status_schema, mode=L.MODE_REFERENCE, device=self.agg.device)
+            self.status_updates_total = GpuCounter(self, "beholder_status_updates_total",
+                                                   "Total number of status messages processed in this processes lifetime",
+                                                   counts=self.status_counts_sibling)
+
+        async def on_status(rmsg):
+            if side_effects is not None:
+                r = side_effects(rmsg)
+                if inspect.isawaitable(r):
+                    await r
+            self.status_agg.push(bytes(rmsg.message.content))
+            rmsg.ack()                                    # index.js:124
+        return on_status
+
+    def status_counts_sibling(self) -> Dict[str, int]:
+        self.status_agg.flush()
+        out = {}
+        for r in self.status_agg.snapshot(0):
+            name = self.status_schema.enum_name(int(r["key_hash"]))
+            if name is not None:
+                out[name.lower()] = int(r["count"])
+        return out
 
     def _ack_upto(self, seq: int) -> int:
         n = 0
@@ -142,6 +177,8 @@ class BeholderGPU:
     def close(self):
         self.commit()
         self.agg.close()
+        if self.status_agg is not None:
+            self.status_agg.close()
 
 
 # --------------------------------------------------------------------------------------------

@@ -67,6 +67,14 @@ def telemetry_progress(progress_kind: int = L.K_INT32) -> Schema:
     )
 
 
+def telemetry_status() -> Schema:
+    """ASSUMED api.TelemetryStatus (index.js:47,63-64 destructures { mediaId, status }): mediaId=1, status=2."""
+    return Schema(
+        fields=[Field("mediaId", 1, L.K_STRING), Field("status", 2, L.K_INT32, L.R_STATUS)],
+        enum=dict(telemetry_progress().enum), type_name="api.TelemetryStatus",
+    )
+
+
 def fill_config(cfg: "L.BhConfig", schema: Schema) -> None:
     if len(schema.fields) > L.BH_MAX_FIELDS:
         raise ValueError("too many fields")

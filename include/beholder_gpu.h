@@ -135,6 +135,10 @@ int bh_snapshot_hist(bh_ctx* ctx, uint64_t window_id, bh_record* out, uint32_t* 
 int bh_list_windows(bh_ctx* ctx, uint64_t* out, uint32_t cap, uint32_t* n);
 /* drop a window's table so its ring slot can be reused */
 int bh_close_window(bh_ctx* ctx, uint64_t window_id);
+/* merge rows (and their histograms, may be NULL) taken earlier with bh_snapshot_hist back into the
+ * tables: restart after a crash, or hand-over between processes.  The reference keeps its counters in
+ * memory only and loses them on restart (index.js:32, "in this processes lifetime"). */
+int bh_restore(bh_ctx* ctx, const bh_record* rows, const uint32_t* hist, uint64_t n);
 /* drops / diagnostics; returns BH_ERR_TABLE_FULL / BH_ERR_WINDOW_RING if events were lost that way */
 int bh_get_counters(bh_ctx* ctx, bh_counters* out);
 
