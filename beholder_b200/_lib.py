@@ -63,7 +63,7 @@ class BhRecord(C.Structure):
 class BhCounters(C.Structure):
     _fields_ = [("events_ok", C.c_uint64), ("dropped_decode", C.c_uint64), ("dropped_enum", C.c_uint64),
                 ("dropped_nan", C.c_uint64), ("dropped_table_full", C.c_uint64), ("dropped_window", C.c_uint64),
-                ("smem_spills", C.c_uint64), ("reserved", C.c_uint64)]
+                ("smem_spills", C.c_uint64), ("slow_decodes", C.c_uint64)]
 
 
 class BhSynthConfig(C.Structure):

@@ -113,6 +113,9 @@ int build_schema(const bh_config& cfg, DevSchema& S) {
       S.fast_value_f64 = f.kind == BH_K_DOUBLE;
     }
   }
+  S.tag_key0 = S.fast_key0 < 16 ? (S.fast_key0 << 3 | 2u) : 0xFFFFFFFFu;
+  S.tag_status = S.fast_status < 16 ? (S.fast_status << 3) : 0xFFFFFFFFu;
+  S.tag_value = S.fast_value < 16 ? (S.fast_value << 3 | (S.fast_value_f64 ? 1u : 0u)) : 0xFFFFFFFFu;
   S.n_parts = parts;
   S.mode = cfg.mode;
   if (const char* d = getenv("BH_DEBUG_SKIP")) S.dbg = (uint32_t)atoi(d);

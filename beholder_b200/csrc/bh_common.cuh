@@ -111,6 +111,7 @@ struct DevSchema {
   uint32_t fast_status_part; // its key part index + 1, or 0
   uint32_t fast_value;       // value when its only role is value and it is int32 or double
   uint32_t fast_value_f64;   // ... and it is a double
+  uint32_t tag_key0, tag_status, tag_value;   // their canonical one-byte tags (0xFFFFFFFF = none)
   uint32_t dbg;              // BH_DEBUG_SKIP (timing experiments): 1 no parse, 2 no hash, 4 no staging
   Div64 wdiv;
 };
@@ -138,7 +139,7 @@ struct DevTables {
   uint32_t hist_buckets;
 };
 
-enum CounterIdx { C_OK = 0, C_DECODE = 1, C_ENUM = 2, C_NAN = 3, C_TABLE_FULL = 4, C_WINDOW = 5, C_SPILL = 6 };
+enum CounterIdx { C_OK = 0, C_DECODE = 1, C_ENUM = 2, C_NAN = 3, C_TABLE_FULL = 4, C_WINDOW = 5, C_SPILL = 6, C_SLOW = 7 };
 
 // ---------------------------------------------------------------------------------------
 // splitmix64 and the synthetic stream, one definition for host and device

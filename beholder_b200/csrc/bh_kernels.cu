@@ -164,16 +164,12 @@ __device__ __forceinline__ int smem_find_or_insert(const SmemTable& M, const Dev
   return smem_insert(M, T, kh, wrel, win, slot, kSmemProbes - p);
 }
 
+// Outcome counters of a CTA.  Only the count of aggregated events lives in a register; drops, spills
+// and slow decodes are rare and go straight to a shared-memory array (keeps 7 registers out of the loop).
 struct LaneCounters {
-  uint32_t c[7];
-  __device__ __forceinline__ void clear() {
-#pragma unroll
-    for (int i = 0; i < 7; i++) c[i] = 0;
-  }
-  __device__ __forceinline__ void bump(uint32_t which) {   // keeps c[] in registers
-#pragma unroll
-    for (int i = 0; i < 7; i++) c[i] += (which == (uint32_t)i);
-  }
+  uint32_t ok;
+  uint32_t* s;     // shared: u32[8], zeroed by the kernel
+  __device__ __forceinline__ void bump(uint32_t which) { atomicAdd(&s[which], 1u); }
 };
 
 // One event into the tables.  `wbase` is the CTA's first window minus one.
@@ -187,7 +183,7 @@ __device__ __forceinline__ void aggregate_event(const DevSchema& S, const DevTab
   int slot = -1;
   if (S.dbg & 16) slot = (int)((((uint32_t)kh ^ (uint32_t)(kh >> 32)) * 0x9E3779B1u) >> M.shift);
   else if (kh < kLockKey && wr < 255ull) slot = smem_find_or_insert(M, T, kh, (uint32_t)wr, win);
-  if (S.dbg & 8) { C.c[C_OK] += (slot >= 0); return; }
+  if (S.dbg & 8) { C.ok += (slot >= 0); return; }
   if (slot >= 0) {
     if (ops & BH_OP_HIST) {
       if (INTV) v = (double)iv;
@@ -212,7 +208,7 @@ __device__ __forceinline__ void aggregate_event(const DevSchema& S, const DevTab
       if (ops & BH_OP_MIN) atomicMax((unsigned long long*)M.vc + slot, (unsigned long long)~ord);
       if (ops & BH_OP_MAX) atomicMax((unsigned long long*)M.vd + slot, (unsigned long long)ord);
     }
-    C.c[C_OK]++;
+    C.ok++;
     return;
   }
   // spill: straight to the HBM table
@@ -225,7 +221,7 @@ __device__ __forceinline__ void aggregate_event(const DevSchema& S, const DevTab
   uint64_t gi = (uint64_t)r * T.stride + gs;
   g_update(T, ops, gi, 1ull, v, ~ord, ord);
   if (ops & BH_OP_HIST) atomicAdd(&T.hist[gi * T.hist_buckets + hist_bucket(bits, T.hist_buckets, S.hist_e0)], 1u);
-  C.c[C_OK]++; C.c[C_SPILL]++;
+  C.ok++; C.bump(C_SPILL);
 }
 
 // CTA end: every shared entry goes to its HBM slot.  Events of an entry whose window or key cannot
@@ -263,14 +259,11 @@ __device__ __forceinline__ void smem_table_flush(const DevSchema& S, const DevTa
   }
 }
 
-__device__ __forceinline__ void counters_flush(const DevTables& T, LaneCounters& C, uint32_t* s_cnt /*[8] zeroed*/) {
-#pragma unroll
-  for (int i = 0; i < 7; i++) {
-    uint32_t v = __reduce_add_sync(0xFFFFFFFFu, C.c[i]);
-    if ((threadIdx.x & 31) == 0 && v) atomicAdd(&s_cnt[i], v);
-  }
+__device__ __forceinline__ void counters_flush(const DevTables& T, LaneCounters& C, uint32_t* s_cnt /*[8]*/) {
+  uint32_t v = __reduce_add_sync(0xFFFFFFFFu, C.ok);
+  if ((threadIdx.x & 31) == 0 && v) atomicAdd(&s_cnt[C_OK], v);
   __syncthreads();
-  if (threadIdx.x < 7 && s_cnt[threadIdx.x]) atomicAdd(&T.counters[threadIdx.x], (unsigned long long)s_cnt[threadIdx.x]);
+  if (threadIdx.x < 8 && s_cnt[threadIdx.x]) atomicAdd(&T.counters[threadIdx.x], (unsigned long long)s_cnt[threadIdx.x]);
 }
 
 // shared-memory access by 32-bit shared-window address, for the staged payload bytes
@@ -519,6 +512,74 @@ __device__ __forceinline__ bool decode_fast(const DevSchema& S, const SmemRd& r,
   return true;
 }
 
+// ---- straight path ------------------------------------------------------------------------------
+// What encoders actually emit for api.TelemetryProgress: fields in number order, each at most once —
+// [key part 0][unknown length-delimited pad]?[status]?[value]? then role-less strings (host) — all with
+// single-byte tags and lengths.  Recognised with a handful of compares against launch constants, no
+// loop over a schema table.  Anything else (other order, repeats, other wire types, long varints, a
+// field with a role in the tail) returns false and the message goes to decode_fast / decode_event, so
+// the outcome is always the general decoder's.  Bytes just past the message may be read (they are
+// inside the warp buffer); every use is guarded by a position check.
+__device__ __forceinline__ bool decode_straight(const DevSchema& S, const SmemRd& r, uint32_t len, Parsed& P) {
+  uint32_t lp = r.off;
+  const uint32_t end = lp + len;
+  uint32_t t = r.ab(lp), n = r.ab(lp + 1);
+  uint32_t kpos = 0, klen = 0, status = 0, uval = 0;
+  double value = 0.0;
+  bool bad = false;
+  // role-less strings (clamped) and unknown length-delimited fields (strict): skipped wherever they stand
+  auto skip_plain = [&]() {
+    while (lp < end) {
+      const uint32_t f = (t & 0x80u) ? 0xFFFFu : S.fld[t >> 3];
+      const bool str = f == (uint32_t)BH_K_STRING, unk = f == 0u && (t & 7u) == 2u;
+      if (!(str || unk)) return;                           // a field with a role (or anything unusual): caller decides
+      if (lp + 2 > end) { bad = true; return; }
+      lp += 2;
+      if (n & 0x80u) {                                     // two-byte length
+        const uint32_t b2 = r.ab(lp);
+        if (lp >= end || (b2 & 0x80u)) { bad = true; return; }
+        n = (n & 0x7Fu) | (b2 << 7);
+        lp += 1;
+      }
+      if (lp + n > end) { if (unk) { bad = true; return; } lp = end; }   // string() clamps, skip() throws
+      else lp += n;
+      t = r.ab(lp); n = r.ab(lp + 1);
+    }
+  };
+  if (lp < end && t == S.tag_key0) {
+    if (lp + 2 > end || (n & 0x80u)) return false;
+    lp += 2;
+    const uint32_t e2 = min(lp + n, end);                  // BufferReader.string() clamps
+    kpos = lp - r.off; klen = e2 - lp; lp = e2;
+    t = r.ab(lp); n = r.ab(lp + 1);
+  }
+  skip_plain();
+  if (bad) return false;
+  if (lp < end && t == S.tag_status) {
+    if (lp + 2 > end || (n & 0x80u)) return false;
+    status = n; lp += 2;
+    t = r.ab(lp); n = r.ab(lp + 1);
+  }
+  if (lp < end && t == S.tag_value) {
+    if (S.fast_value_f64) {
+      if (lp + 9 > end) return false;
+      value = __longlong_as_double((long long)r.le64(lp + 1 - r.off, 8)); lp += 9;
+    } else {
+      if (lp + 2 > end || (n & 0x80u)) return false;
+      uval = n; lp += 2;
+    }
+    t = r.ab(lp); n = r.ab(lp + 1);
+  }
+  skip_plain();
+  if (bad || lp < end) return false;                       // something with a role is left: not the canonical order
+  P.clear();
+  P.ppos[0] = kpos; P.plen[0] = klen; P.status = status; P.uval = uval; P.value = value;
+  if (S.fast_status_part == 1) P.pval[0] = status;
+  if (S.fast_status_part == 2) P.pval[1] = status;
+  if (S.fast_status_part == 3) P.pval[2] = status;
+  return true;
+}
+
 __device__ __forceinline__ uint64_t hash_span_smem(const SmemRd& r, uint32_t lp, uint32_t n, uint32_t field, uint64_t h) {
   uint32_t a = lp & ~3u;
   const uint32_t sh = (lp & 3u) * 8u;
@@ -564,17 +625,24 @@ __device__ __forceinline__ uint32_t finish_event(const DevSchema& S, const Parse
   return BH_EV_OK;
 }
 
+constexpr uint32_t kSlowDecode = 0x100u;   // outcome flag: the message left the straight path (diagnostic counter)
+__device__ __noinline__ bool decode_slow(const DevSchema& S, const SmemRd& r, uint32_t len, Parsed& P) {
+  return decode_fast(S, r, len, P) || decode_event(S, r, len, P);
+}
+
 __device__ __forceinline__ uint32_t decode_and_check_smem(const DevSchema& S, const SmemRd& r, uint32_t len, uint64_t& kh,
                                                           double& value, int32_t& ival, uint32_t& status) {
   Parsed P;
   if (S.dbg & 1) { kh = r.off + len; value = 0.0; ival = (int32_t)len; status = 0; return BH_EV_OK; }
-  if (!decode_fast(S, r, len, P)) {
+  uint32_t slow = 0;
+  if (!decode_straight(S, r, len, P)) {
     Parsed Q;   // a separate object: P must not escape into the out-of-line slow path (it would live in local memory)
-    if (!decode_event(S, r, len, Q)) { kh = 0; value = 0.0; ival = 0; status = 0; return BH_EV_DROP_DECODE; }
+    if (!decode_slow(S, r, len, Q)) { kh = 0; value = 0.0; ival = 0; status = 0; return BH_EV_DROP_DECODE | kSlowDecode; }
     P = Q;
+    slow = kSlowDecode;
   }
   kh = (S.dbg & 2) ? (uint64_t)P.ppos[0] * 0x9E3779B97F4A7C15ull + P.status : event_key_hash_smem(S, r, P);
-  return finish_event(S, P, value, ival, status);
+  return finish_event(S, P, value, ival, status) | slow;
 }
 
 __device__ __noinline__ uint32_t decode_and_check_gmem(const DevSchema& S, const uint8_t* p, uint32_t len, uint64_t& kh,
@@ -689,6 +757,8 @@ struct AggSink {
     if (S.has_window && ts && lane < 2) prefetch_l2(ts + e2 + lane * 16);
   }
   __device__ __forceinline__ void event(uint32_t e, uint32_t outcome, uint64_t kh, double value, int32_t ival, uint32_t) {
+    if (outcome & kSlowDecode) C.bump(C_SLOW);
+    outcome &= 0xFFu;
     if (outcome != BH_EV_OK) { C.bump(outcome); return; }
     uint64_t win = 0;
     if (S.has_window) win = div64(ts ? ts[e] : 0ull, S.wdiv);
@@ -711,7 +781,7 @@ k_process_raw(const __grid_constant__ DevSchema S, const __grid_constant__ DevTa
   if (threadIdx.x < 8) s_cnt[threadIdx.x] = 0;
   __syncthreads();
   const uint32_t cs = min(n, blockIdx.x * chunk), ce = min(n, cs + chunk);
-  LaneCounters C; C.clear();
+  LaneCounters C{0u, s_cnt};
   uint64_t wbase = 0;
   if (cs < ce) {
     if (S.has_window) { uint64_t w0 = div64(ts ? ts[cs] : 0ull, S.wdiv); wbase = w0 ? w0 - 1 : 0; }
@@ -729,6 +799,7 @@ struct ColumnSink {
   __device__ __forceinline__ void prefetch(uint32_t, uint32_t) const {}
   __device__ __forceinline__ void event(uint32_t e, uint32_t oc, uint64_t k, double v, int32_t iv, uint32_t st) {
     // integer value kinds: the fast path leaves `v` unset; (double)(int32) is the JS number
+    oc &= 0xFFu;
     const bool have = oc != BH_EV_DROP_DECODE;
     kh[e] = k; val[e] = have && S.int_values ? (double)iv : v; status[e] = (int32_t)st; outcome[e] = (uint8_t)oc;
   }
@@ -762,7 +833,7 @@ k_process_columns(const __grid_constant__ DevSchema S, const __grid_constant__ D
   if (threadIdx.x < 8) s_cnt[threadIdx.x] = 0;
   __syncthreads();
   const uint64_t cs = min(n, (uint64_t)blockIdx.x * chunk), ce = min(n, cs + chunk);
-  LaneCounters C; C.clear();
+  LaneCounters C{0u, s_cnt};
   uint64_t wbase = 0;
   if (cs < ce && S.has_window) { uint64_t w0 = div64(ts[cs], S.wdiv); wbase = w0 ? w0 - 1 : 0; }
   const bool need_value = (S.ops & (BH_OP_SUM | BH_OP_MIN | BH_OP_MAX | BH_OP_HIST)) != 0;

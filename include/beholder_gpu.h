@@ -97,7 +97,7 @@ typedef struct bh_counters {
   uint64_t dropped_table_full; /* -> BH_ERR_TABLE_FULL */
   uint64_t dropped_window;     /* -> BH_ERR_WINDOW_RING */
   uint64_t smem_spills;        /* events that bypassed the shared-memory table (diagnostic) */
-  uint64_t reserved;
+  uint64_t slow_decodes;       // messages that left the decoder's straight path (diagnostic)
 } bh_counters;
 
 typedef struct bh_ctx bh_ctx;

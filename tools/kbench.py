@@ -37,7 +37,7 @@ ds = torch.empty(n, dtype=torch.int32, device="cuda"); do = torch.empty(n, dtype
 out["decode_ms"] = timeit(lambda: g.decode_device(p, o, n, dk, dv, ds, do, stream=s))
 out["columns_ms"] = timeit(lambda: g.process_columns_device(kh, ts, val, n, stream=s))
 out["fused_ms"] = timeit(lambda: g.process_device(p, o, t, n, stream=s))
-k = g.counters(check=False); out["spill_frac"] = k["smem_spills"] / max(1, k["events_ok"]); out["counters"] = k
+k = g.counters(check=False); out["spill_frac"] = k["smem_spills"] / max(1, k["events_ok"]); out["counters"] = k; out["slow_frac"] = k["slow_decodes"] / max(1, k["events_ok"])
 r = bh.Aggregator(schema, mode=L.MODE_REFERENCE)
 out["reference_mode_ms"] = timeit(lambda: r.process_device(p, o, None, n, stream=s))
 for key in ("decode_ms", "columns_ms", "fused_ms", "reference_mode_ms"):
