@@ -15,8 +15,8 @@ const ROLE = { key: 1, status: 2, value: 4 }
 
 // packs a bh_config (include/beholder_gpu.h); offsets follow the C struct layout (little endian)
 function packConfig ({ schema, statusEnum, device = 0 }) {
-  const buf = Buffer.alloc(592)
-  buf.writeUInt32LE(592, 0)            // struct_size
+  const buf = Buffer.alloc(600)
+  buf.writeUInt32LE(600, 0)            // struct_size
   buf.writeInt32LE(device, 4)
   buf.writeUInt32LE(0, 8)              // mode = BH_MODE_REFERENCE
   buf.writeUInt32LE(1, 12)             // ops  = COUNT

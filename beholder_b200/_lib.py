@@ -51,7 +51,7 @@ class BhConfig(C.Structure):
         ("hist_e0", C.c_int32), ("n_fields", C.c_uint32), ("fields", BhField * BH_MAX_FIELDS),
         ("n_enum", C.c_uint32), ("enum_numbers", C.c_int32 * BH_MAX_ENUM),
         ("table_capacity", C.c_uint64), ("hash_seed", C.c_uint64), ("slab_bytes", C.c_uint64),
-        ("slab_events", C.c_uint32), ("n_slabs", C.c_uint32),
+        ("slab_events", C.c_uint32), ("n_slabs", C.c_uint32), ("message_bytes_hint", C.c_uint32), ("reserved0", C.c_uint32),
     ]
 
 

@@ -116,6 +116,7 @@ int build_schema(const bh_config& cfg, DevSchema& S) {
   S.tag_key0 = S.fast_key0 < 16 ? (S.fast_key0 << 3 | 2u) : 0xFFFFFFFFu;
   S.tag_status = S.fast_status < 16 ? (S.fast_status << 3) : 0xFFFFFFFFu;
   S.tag_value = S.fast_value < 16 ? (S.fast_value << 3 | (S.fast_value_f64 ? 1u : 0u)) : 0xFFFFFFFFu;
+  S.big_messages = cfg.message_bytes_hint > 72;
   S.n_parts = parts;
   S.mode = cfg.mode;
   if (const char* d = getenv("BH_DEBUG_SKIP")) S.dbg = (uint32_t)atoi(d);
@@ -182,10 +183,12 @@ int slab_acquire(bh_ctx* c, uint32_t i) {
 
 // launch the fused kernel over what slab `s` holds on the device; `virt` is the payload base the
 // offsets are relative to
-int slab_launch(bh_ctx* c, Slab& s, const uint8_t* virt, uint32_t n, bool with_ts, cudaStream_t copy_stream) {
+int slab_launch(bh_ctx* c, Slab& s, const uint8_t* virt, uint32_t n, bool with_ts, cudaStream_t copy_stream, uint64_t bytes) {
   CU(c, cudaEventRecord(s.copied, copy_stream));
   CU(c, cudaStreamWaitEvent(c->st_compute, s.copied, 0));
-  CU(c, launch_process_raw(c->S, c->T, c->G, virt, s.d_offsets, with_ts ? s.d_ts : nullptr, n, c->st_compute, &c->launches));
+  // the ingest path knows the slab's byte count: pick the kernel variant from the real average size
+  CU(c, launch_process_raw(c->S, c->T, c->G, virt, s.d_offsets, with_ts ? s.d_ts : nullptr, n, c->st_compute, &c->launches,
+                           n && bytes / n > 72 ? 1 : 0));
   CU(c, cudaEventRecord(s.done, c->st_compute));
   s.in_flight = true;
   s.seq_end = c->pushed;
@@ -201,7 +204,7 @@ int submit_current(bh_ctx* c) {
   CU(c, cudaMemcpyAsync(s.d_offsets, s.h_offsets, ((size_t)s.n + 1) * 4, cudaMemcpyHostToDevice, cs));
   bool with_ts = c->S.has_window;
   if (with_ts) CU(c, cudaMemcpyAsync(s.d_ts, s.h_ts, (size_t)s.n * 8, cudaMemcpyHostToDevice, cs));
-  int rc = slab_launch(c, s, s.d_payload, s.n, with_ts, cs);
+  int rc = slab_launch(c, s, s.d_payload, s.n, with_ts, cs, s.bytes);
   if (rc) return rc;
   s.n = 0; s.bytes = 0; s.h_offsets[0] = 0;
   c->cur = (c->cur + 1) % (uint32_t)c->slabs.size();
@@ -409,7 +412,7 @@ int bh_push_batch_pinned(bh_ctx* c, const uint8_t* slab, const uint32_t* off, co
     c->pushed += j - i;
     // offsets stay absolute: hand the kernel the (16-byte aligned) address offset 0 would have
     const uint8_t* virt = s.d_payload + head - off[i];
-    rc = slab_launch(c, s, virt, j - i, with_ts, cs);
+    rc = slab_launch(c, s, virt, j - i, with_ts, cs, nb);
     if (rc) return rc;
     c->cur = (c->cur + 1) % (uint32_t)c->slabs.size();
     i = j;

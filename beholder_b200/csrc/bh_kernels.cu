@@ -671,12 +671,31 @@ __device__ __forceinline__ uint4 ldg_stream(const uint4* p) {
 }
 __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" :: "l"(p)); }
 
+// coalesced copy of payload[A, B) (both multiples of 16) into the skewed warp buffer
+__device__ __forceinline__ void stage_range(const uint8_t* __restrict__ payload, uint32_t A, uint32_t B, uint32_t wb,
+                                            uint32_t lane, uint32_t dbg) {
+  const uint4* src = reinterpret_cast<const uint4*>(payload + A);
+  const uint32_t nvec = (B - A) >> 4;
+  uint4 v[kWarpChunks];
+#pragma unroll
+  for (uint32_t k = 0; k < kWarpChunks; k++)
+    if (lane + 32 * k < nvec && !(dbg & 4)) v[k] = ldg_stream(src + lane + 32 * k);
+#pragma unroll
+  for (uint32_t k = 0; k < kWarpChunks; k++) {
+    const uint32_t i = lane + 32 * k;
+    if (i < nvec) {
+      const uint32_t d = wb + skew(i << 4);   // a 16-byte chunk never straddles a 64-byte block
+      sts32(d, v[k].x); sts32(d + 4, v[k].y); sts32(d + 8, v[k].z); sts32(d + 12, v[k].w);
+    }
+  }
+}
+
 // Handler interface shared by the fused and the decode-only kernel.  Each warp takes batches of 32
 // consecutive messages, copies their bytes (one contiguous range) into its shared buffer with
 // coalesced 128-bit loads, then every lane parses its own message.  The offsets of the NEXT batch are
 // loaded before the current one is parsed, and the lines the batch after that will touch are
 // prefetched into L2, so a warp rarely waits for HBM.
-template <class Sink>
+template <bool BIG, class Sink>
 __device__ __forceinline__ void raw_warp_loop(const DevSchema& S, const uint8_t* __restrict__ payload,
                                               const uint32_t* __restrict__ offsets, uint32_t cs, uint32_t ce,
                                               uint32_t wb, Sink& sink) {
@@ -704,48 +723,34 @@ __device__ __forceinline__ void raw_warp_loop(const DevSchema& S, const uint8_t*
         if (lane < 18 && guess >= first && guess < total16) prefetch_l2(payload + guess);
       }
     }
-    const uint32_t cnt = min(32u, ce - e0);
-    uint32_t done = 0;
-    while (done < cnt) {
-      const uint32_t b0 = __shfl_sync(0xFFFFFFFFu, o0, done);
-      const uint32_t A = b0 & ~15u;
-      const bool fits = valid && lane >= done && o1 >= o0 && o0 >= A && (o1 - A) <= kWarpBuf;
-      const uint32_t mask = __ballot_sync(0xFFFFFFFFu, fits) >> done;
-      uint32_t m = mask == 0xFFFFFFFFu ? 32u : (uint32_t)__ffs(~mask) - 1u;   // leading run of lanes that fit
-      uint32_t outcome; uint64_t kh; double value; int32_t ival; uint32_t status;
-      bool mine;
-      if (m == 0) {                    // a single oversized (or inconsistent) message: parse from global
-        m = 1;
-        mine = lane == done;
-        if (mine) {
-          if (o1 < o0) { outcome = BH_EV_DROP_DECODE; kh = 0; value = 0.0; ival = 0; status = 0; }
-          else outcome = decode_and_check_gmem(S, payload + o0, o1 - o0, kh, value, ival, status);
-        }
-      } else {
-        const uint32_t bend = __shfl_sync(0xFFFFFFFFu, o1, done + m - 1);
-        const uint32_t B = min((bend + 15u) & ~15u, total16);
-        const uint4* src = reinterpret_cast<const uint4*>(payload + A);
-        const uint32_t nvec = (B - A) >> 4;
-        uint4 v[kWarpChunks];
+    // A batch is one contiguous byte range, staged in the warp buffer and parsed from shared memory.
+    // BIG = false (messages up to ~72 B expected): the batch is staged whole; a batch that does not fit
+    // is parsed from global memory, every lane its own message.  BIG = true: a batch may also be staged
+    // in 2 parts of 16 messages (up to 144 B each) or 4 parts of 8 (up to 288 B) before falling back to
+    // global memory.  Same results either way; the host picks the variant from the message-size hint.
+    const bool sane = !valid || o1 >= o0;
+    uint32_t outcome = BH_EV_DROP_DECODE; uint64_t kh = 0; double value = 0.0; int32_t ival = 0; uint32_t status = 0;
+    uint32_t parts = 0;
 #pragma unroll
-        for (uint32_t k = 0; k < kWarpChunks; k++)
-          if (lane + 32 * k < nvec && !(S.dbg & 4)) v[k] = ldg_stream(src + lane + 32 * k);
-#pragma unroll
-        for (uint32_t k = 0; k < kWarpChunks; k++) {
-          const uint32_t i = lane + 32 * k;
-          if (i < nvec) {
-            const uint32_t d = wb + skew(i << 4);   // a 16-byte chunk never straddles a 64-byte block
-            sts32(d, v[k].x); sts32(d + 4, v[k].y); sts32(d + 8, v[k].z); sts32(d + 12, v[k].w);
-          }
-        }
-        __syncwarp();
-        mine = lane >= done && lane < done + m;
-        if (mine) { SmemRd r{wb, o0 - A}; outcome = decode_and_check_smem(S, r, o1 - o0, kh, value, ival, status); }
-      }
-      if (mine) sink.event(e, outcome, kh, value, ival, status);
-      __syncwarp();
-      done += m;
+    for (uint32_t g = 32; g >= (BIG ? 8u : 32u) && parts == 0; g >>= 1) {
+      const uint32_t ga = __shfl_sync(0xFFFFFFFFu, o0, lane & ~(g - 1)) & ~15u;
+      if (__all_sync(0xFFFFFFFFu, !valid || (sane && o0 >= ga && (o1 - ga) <= kWarpBuf))) parts = 32 / g;
     }
+    if (parts) {
+      const uint32_t g = 32 / parts, cnt = min(32u, ce - e0);
+      for (uint32_t q = 0; q * g < cnt; q++) {
+        const uint32_t A = __shfl_sync(0xFFFFFFFFu, o0, q * g) & ~15u;
+        const uint32_t bend = __shfl_sync(0xFFFFFFFFu, o1, min(q * g + g, cnt) - 1);
+        stage_range(payload, A, min((bend + 15u) & ~15u, total16), wb, lane, S.dbg);
+        __syncwarp();
+        if (valid && (!BIG || (lane / g) == q)) { SmemRd r{wb, o0 - A}; outcome = decode_and_check_smem(S, r, o1 - o0, kh, value, ival, status); }
+        __syncwarp();                               // the buffer is rewritten by the next part / batch
+        if (!BIG) break;
+      }
+    } else if (valid && sane) {
+      outcome = decode_and_check_gmem(S, payload + o0, o1 - o0, kh, value, ival, status);
+    }
+    if (valid) sink.event(e, outcome, kh, value, ival, status);
   }
 }
 
@@ -766,7 +771,7 @@ struct AggSink {
   }
 };
 
-template <bool INTV>
+template <bool INTV, bool BIG>
 __global__ void __launch_bounds__(INTV ? kRawThreads : kRawThreadsF64, 1)
 k_process_raw(const __grid_constant__ DevSchema S, const __grid_constant__ DevTables T,
               const uint8_t* __restrict__ payload, const uint32_t* __restrict__ offsets,
@@ -786,7 +791,7 @@ k_process_raw(const __grid_constant__ DevSchema S, const __grid_constant__ DevTa
   if (cs < ce) {
     if (S.has_window) { uint64_t w0 = div64(ts ? ts[cs] : 0ull, S.wdiv); wbase = w0 ? w0 - 1 : 0; }
     AggSink<INTV> sink{S, T, M, ts, wbase, C};
-    raw_warp_loop(S, payload, offsets, cs, ce, wb, sink);
+    raw_warp_loop<BIG>(S, payload, offsets, cs, ce, wb, sink);
   }
   __syncthreads();
   smem_table_flush<INTV>(S, T, M, wbase);
@@ -805,6 +810,7 @@ struct ColumnSink {
   }
 };
 
+template <bool BIG>
 __global__ void __launch_bounds__(kRawThreads, 1)
 k_decode(const __grid_constant__ DevSchema S, const uint8_t* __restrict__ payload,
          const uint32_t* __restrict__ offsets, uint32_t n, uint32_t chunk, uint64_t* kh, double* val,
@@ -814,7 +820,7 @@ k_decode(const __grid_constant__ DevSchema S, const uint8_t* __restrict__ payloa
   const uint32_t cs = min(n, blockIdx.x * chunk), ce = min(n, cs + chunk);
   if (cs >= ce) return;
   ColumnSink sink{S, kh, val, status, outcome};
-  raw_warp_loop(S, payload, offsets, cs, ce, wb, sink);
+  raw_warp_loop<BIG>(S, payload, offsets, cs, ce, wb, sink);
 }
 
 // =========================================================================================
@@ -965,13 +971,14 @@ __global__ void k_close_release(const __grid_constant__ DevTables T, uint64_t wi
 // once per device, with that device current (bh_create)
 cudaError_t configure_kernels(const LaunchGeom& G) {
   int dyn = G.smem_optin - 1024;   // leave room for the kernels' static shared memory
-  cudaError_t e = cudaFuncSetAttribute(k_process_raw<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn);
-  if (e != cudaSuccess) return e;
-  e = cudaFuncSetAttribute(k_process_raw<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn);
-  if (e != cudaSuccess) return e;
-  e = cudaFuncSetAttribute(k_decode, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn);
-  if (e != cudaSuccess) return e;
-  return cudaFuncSetAttribute(k_process_columns, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn);
+  const void* fns[] = {(const void*)k_process_raw<true, false>, (const void*)k_process_raw<true, true>,
+                       (const void*)k_process_raw<false, false>, (const void*)k_process_raw<false, true>,
+                       (const void*)k_decode<false>, (const void*)k_decode<true>, (const void*)k_process_columns};
+  for (const void* f : fns) {
+    cudaError_t e = cudaFuncSetAttribute(f, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn);
+    if (e != cudaSuccess) return e;
+  }
+  return cudaSuccess;
 }
 
 static uint32_t pick_smem_slots(bool intv, bool hist, const LaunchGeom& G, size_t other_bytes) {
@@ -983,7 +990,7 @@ static uint32_t pick_smem_slots(bool intv, bool hist, const LaunchGeom& G, size_
 
 cudaError_t launch_process_raw(const DevSchema& S, const DevTables& T, const LaunchGeom& G,
                                const uint8_t* payload, const uint32_t* offsets, const uint64_t* ts,
-                               uint32_t n, cudaStream_t st, int* launches) {
+                               uint32_t n, cudaStream_t st, int* launches, int big_override) {
   if (n == 0) return cudaSuccess;
   const bool hist = (S.ops & BH_OP_HIST) != 0, intv = S.int_values != 0;
   const uint32_t threads = intv ? kRawThreads : kRawThreadsF64;
@@ -995,8 +1002,11 @@ cudaError_t launch_process_raw(const DevSchema& S, const DevTables& T, const Lau
   if (need < grid) grid = need;
   uint32_t chunk = (n + grid - 1) / grid;
   chunk = (chunk + 31u) & ~31u;
-  if (intv) k_process_raw<true><<<grid, kRawThreads, smem, st>>>(S, T, payload, offsets, ts, n, chunk, ns);
-  else k_process_raw<false><<<grid, kRawThreadsF64, smem, st>>>(S, T, payload, offsets, ts, n, chunk, ns);
+  const bool big = big_override < 0 ? S.big_messages != 0 : big_override != 0;
+  if (intv && !big) k_process_raw<true, false><<<grid, kRawThreads, smem, st>>>(S, T, payload, offsets, ts, n, chunk, ns);
+  else if (intv) k_process_raw<true, true><<<grid, kRawThreads, smem, st>>>(S, T, payload, offsets, ts, n, chunk, ns);
+  else if (!big) k_process_raw<false, false><<<grid, kRawThreadsF64, smem, st>>>(S, T, payload, offsets, ts, n, chunk, ns);
+  else k_process_raw<false, true><<<grid, kRawThreadsF64, smem, st>>>(S, T, payload, offsets, ts, n, chunk, ns);
   if (launches) (*launches)++;
   return cudaGetLastError();
 }
@@ -1011,7 +1021,8 @@ cudaError_t launch_decode(const DevSchema& S, const LaunchGeom& G, const uint8_t
   if (need < grid) grid = need;
   uint32_t chunk = (n + grid - 1) / grid;
   chunk = (chunk + 31u) & ~31u;
-  k_decode<<<grid, kRawThreads, smem, st>>>(S, payload, offsets, n, chunk, kh, val, status, outcome);
+  if (S.big_messages) k_decode<true><<<grid, kRawThreads, smem, st>>>(S, payload, offsets, n, chunk, kh, val, status, outcome);
+  else k_decode<false><<<grid, kRawThreads, smem, st>>>(S, payload, offsets, n, chunk, kh, val, status, outcome);
   return cudaGetLastError();
 }
 

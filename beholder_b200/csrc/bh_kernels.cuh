@@ -12,7 +12,8 @@ struct LaunchGeom {
 // fused proto.decode + enum check + aggregate over one raw batch (index.js:129-138)
 cudaError_t launch_process_raw(const DevSchema& S, const DevTables& T, const LaunchGeom& G,
                                const uint8_t* payload, const uint32_t* offsets, const uint64_t* ts,
-                               uint32_t n, cudaStream_t st, int* launches);
+                               uint32_t n, cudaStream_t st, int* launches, int big_override = -1);
+// big_override: -1 = follow the schema's message-size hint, 0 / 1 = small / large message kernels
 // aggregate pre-decoded columns
 cudaError_t launch_process_columns(const DevSchema& S, const DevTables& T, const LaunchGeom& G,
                                    const uint64_t* kh, const uint64_t* ts, const double* val,

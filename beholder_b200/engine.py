@@ -42,7 +42,7 @@ class Aggregator:
                  window_ms: int = 10_000, window_ring: int = 0, table_capacity: int = 0,
                  hist_buckets: int = 64, hist_e0: int = DEFAULT_HIST_E0, hash_seed: int = 0xBE401DE5,
                  device: int = 0, slab_bytes: int = 0, slab_events: int = 0, n_slabs: int = 0,
-                 enum_drop: bool = True):
+                 enum_drop: bool = True, message_bytes_hint: int = 0):
         schema = schema or telemetry_progress()
         if mode == L.MODE_WINDOWED:
             schema = schema.with_roles(key=key)
@@ -61,6 +61,7 @@ class Aggregator:
         cfg.slab_bytes = slab_bytes
         cfg.slab_events = slab_events
         cfg.n_slabs = n_slabs
+        cfg.message_bytes_hint = message_bytes_hint
         fill_config(cfg, schema)
         if not enum_drop:
             cfg.n_enum = 0

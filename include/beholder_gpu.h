@@ -80,6 +80,9 @@ typedef struct bh_config {
   uint64_t slab_bytes;         /* ingest ring: payload bytes per slab (0 -> 64 MiB) */
   uint32_t slab_events;        /* ingest ring: events per slab (0 -> 1 Mi) */
   uint32_t n_slabs;            /* ingest ring depth (0 -> 3) */
+  uint32_t message_bytes_hint; /* typical serialized message size; above 72 selects the kernels that stage
+                                * larger messages (results do not depend on it); 0 = small messages */
+  uint32_t reserved0;
 } bh_config;
 
 /* One aggregate row.  REFERENCE mode: key_hash = status number, window_id = 0, count = the value of

@@ -75,13 +75,15 @@ def test_device_generator_equals_host_generator():
     assert np.array_equal(p.cpu().numpy()[:total], slab[:total])
 
 
-@pytest.mark.parametrize("payload_bytes", [0, 64, 200, 1024, 4096])
-def test_reference_counts_on_device_resident_batches(payload_bytes):
+@pytest.mark.parametrize("hinted", [False, True])
+@pytest.mark.parametrize("payload_bytes", [0, 64, 100, 200, 1024, 4096])
+def test_reference_counts_on_device_resident_batches(payload_bytes, hinted):
     import torch
     spec = SynthSpec(n_keys=1000, rate_per_ms=50, malformed_ppm=10000, unknown_enum_ppm=10000, payload_bytes=payload_bytes)
     n = 200_000 if payload_bytes <= 200 else 30_000
     p, o, t, total = generate_device(spec, 0, n)
-    with bh.Aggregator(mode=L.MODE_REFERENCE) as g:
+    # the message-size hint only selects a kernel variant (batches staged whole / in parts): same results
+    with bh.Aggregator(mode=L.MODE_REFERENCE, message_bytes_hint=payload_bytes if hinted else 0) as g:
         g.process_device(p, o, None, n)
         g.sync()
         counts = g.status_counts()

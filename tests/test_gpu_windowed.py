@@ -48,6 +48,15 @@ def test_c2_shape_count_sum_min_max(zipf, f64):
     assert len(np.unique(got["window_id"])) >= 10
 
 
+@pytest.mark.parametrize("payload_bytes,hint", [(100, 100), (160, 160), (300, 300), (160, 0)])
+def test_larger_messages_windowed(payload_bytes, hint):
+    spec = SynthSpec(n_keys=500, rate_per_ms=10, payload_bytes=payload_bytes, value_f64=True, malformed_ppm=5000)
+    got, a, k = _run_raw(spec, 150_000, ALL_OPS, table_capacity=1024, message_bytes_hint=hint)
+    assert_records_equal(got, a.snapshot(), ALL_OPS)
+    d = a.dropped()
+    assert (k["dropped_decode"], k["dropped_enum"]) == (d["decode"], d["enum"])
+
+
 def test_histograms_and_spill_many_keys():
     # config 3 shape at reduced size: more keys than the shared-memory table holds, log2 histograms
     ops = ALL_OPS | L.OP_HIST

@@ -31,14 +31,14 @@ def timeit(fn):
     return e0.elapsed_time(e1) / a.reps
 
 out = {"events": n, "bytes": total + 12 * n, "args": vars(a)}
-g = bh.Aggregator(schema, mode=L.MODE_WINDOWED, ops=ops, table_capacity=a.cap, window_ring=32)
+g = bh.Aggregator(schema, mode=L.MODE_WINDOWED, ops=ops, table_capacity=a.cap, window_ring=32, message_bytes_hint=a.payload)
 dk = torch.empty(n, dtype=torch.int64, device="cuda"); dv = torch.empty(n, dtype=torch.float64, device="cuda")
 ds = torch.empty(n, dtype=torch.int32, device="cuda"); do = torch.empty(n, dtype=torch.uint8, device="cuda")
 out["decode_ms"] = timeit(lambda: g.decode_device(p, o, n, dk, dv, ds, do, stream=s))
 out["columns_ms"] = timeit(lambda: g.process_columns_device(kh, ts, val, n, stream=s))
 out["fused_ms"] = timeit(lambda: g.process_device(p, o, t, n, stream=s))
 k = g.counters(check=False); out["spill_frac"] = k["smem_spills"] / max(1, k["events_ok"]); out["counters"] = k; out["slow_frac"] = k["slow_decodes"] / max(1, k["events_ok"])
-r = bh.Aggregator(schema, mode=L.MODE_REFERENCE)
+r = bh.Aggregator(schema, mode=L.MODE_REFERENCE, message_bytes_hint=a.payload)
 out["reference_mode_ms"] = timeit(lambda: r.process_device(p, o, None, n, stream=s))
 for key in ("decode_ms", "columns_ms", "fused_ms", "reference_mode_ms"):
     out[key.replace("_ms", "_Gev_s")] = n / out[key] / 1e6
