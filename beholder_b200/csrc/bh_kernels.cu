@@ -520,64 +520,72 @@ __device__ __forceinline__ bool decode_fast(const DevSchema& S, const SmemRd& r,
 // field with a role in the tail) returns false and the message goes to decode_fast / decode_event, so
 // the outcome is always the general decoder's.  Bytes just past the message may be read (they are
 // inside the warp buffer); every use is guarded by a position check.
-__device__ __forceinline__ bool decode_straight(const DevSchema& S, const SmemRd& r, uint32_t len, Parsed& P) {
+// `mask` = the lanes that call it together.  The optional sections make lanes of one warp diverge (some
+// messages carry a pad or a host field, some do not); the explicit __syncwarp(mask) after each section
+// brings them back together — without it the compiler reconverges only at the end and the rest of the
+// decoder plus the key hash run once per divergent group (measured: 40 % slower on mixed streams).
+// Hence no early return before the last section: failures are carried in `ok`.
+__device__ __forceinline__ bool decode_straight(const DevSchema& S, const SmemRd& r, uint32_t len, Parsed& P, uint32_t mask) {
   uint32_t lp = r.off;
   const uint32_t end = lp + len;
   uint32_t t = r.ab(lp), n = r.ab(lp + 1);
   uint32_t kpos = 0, klen = 0, status = 0, uval = 0;
   double value = 0.0;
-  bool bad = false;
+  bool ok = true;
   // role-less strings (clamped) and unknown length-delimited fields (strict): skipped wherever they stand
   auto skip_plain = [&]() {
-    while (lp < end) {
+    while (ok && lp < end) {
       const uint32_t f = (t & 0x80u) ? 0xFFFFu : S.fld[t >> 3];
       const bool str = f == (uint32_t)BH_K_STRING, unk = f == 0u && (t & 7u) == 2u;
-      if (!(str || unk)) return;                           // a field with a role (or anything unusual): caller decides
-      if (lp + 2 > end) { bad = true; return; }
+      if (!(str || unk)) break;                            // a field with a role (or anything unusual): caller decides
+      if (lp + 2 > end) { ok = false; break; }
       lp += 2;
       if (n & 0x80u) {                                     // two-byte length
         const uint32_t b2 = r.ab(lp);
-        if (lp >= end || (b2 & 0x80u)) { bad = true; return; }
+        if (lp >= end || (b2 & 0x80u)) { ok = false; break; }
         n = (n & 0x7Fu) | (b2 << 7);
         lp += 1;
       }
-      if (lp + n > end) { if (unk) { bad = true; return; } lp = end; }   // string() clamps, skip() throws
+      if (lp + n > end) { if (unk) { ok = false; break; } lp = end; }   // string() clamps, skip() throws
       else lp += n;
       t = r.ab(lp); n = r.ab(lp + 1);
     }
   };
   if (lp < end && t == S.tag_key0) {
-    if (lp + 2 > end || (n & 0x80u)) return false;
-    lp += 2;
-    const uint32_t e2 = min(lp + n, end);                  // BufferReader.string() clamps
-    kpos = lp - r.off; klen = e2 - lp; lp = e2;
-    t = r.ab(lp); n = r.ab(lp + 1);
+    if (lp + 2 > end || (n & 0x80u)) ok = false;
+    else {
+      lp += 2;
+      const uint32_t e2 = min(lp + n, end);                // BufferReader.string() clamps
+      kpos = lp - r.off; klen = e2 - lp; lp = e2;
+      t = r.ab(lp); n = r.ab(lp + 1);
+    }
   }
+  __syncwarp(mask);
   skip_plain();
-  if (bad) return false;
-  if (lp < end && t == S.tag_status) {
-    if (lp + 2 > end || (n & 0x80u)) return false;
-    status = n; lp += 2;
-    t = r.ab(lp); n = r.ab(lp + 1);
+  __syncwarp(mask);
+  if (ok && lp < end && t == S.tag_status) {
+    if (lp + 2 > end || (n & 0x80u)) ok = false;
+    else { status = n; lp += 2; t = r.ab(lp); n = r.ab(lp + 1); }
   }
-  if (lp < end && t == S.tag_value) {
+  if (ok && lp < end && t == S.tag_value) {
     if (S.fast_value_f64) {
-      if (lp + 9 > end) return false;
-      value = __longlong_as_double((long long)r.le64(lp + 1 - r.off, 8)); lp += 9;
+      if (lp + 9 > end) ok = false;
+      else { value = __longlong_as_double((long long)r.le64(lp + 1 - r.off, 8)); lp += 9; }
     } else {
-      if (lp + 2 > end || (n & 0x80u)) return false;
-      uval = n; lp += 2;
+      if (lp + 2 > end || (n & 0x80u)) ok = false;
+      else { uval = n; lp += 2; }
     }
     t = r.ab(lp); n = r.ab(lp + 1);
   }
+  __syncwarp(mask);
   skip_plain();
-  if (bad || lp < end) return false;                       // something with a role is left: not the canonical order
+  __syncwarp(mask);
   P.clear();
   P.ppos[0] = kpos; P.plen[0] = klen; P.status = status; P.uval = uval; P.value = value;
   if (S.fast_status_part == 1) P.pval[0] = status;
   if (S.fast_status_part == 2) P.pval[1] = status;
   if (S.fast_status_part == 3) P.pval[2] = status;
-  return true;
+  return ok && lp == end;                                  // something with a role is left: not the canonical order
 }
 
 __device__ __forceinline__ uint64_t hash_span_smem(const SmemRd& r, uint32_t lp, uint32_t n, uint32_t field, uint64_t h) {
@@ -631,11 +639,11 @@ __device__ __noinline__ bool decode_slow(const DevSchema& S, const SmemRd& r, ui
 }
 
 __device__ __forceinline__ uint32_t decode_and_check_smem(const DevSchema& S, const SmemRd& r, uint32_t len, uint64_t& kh,
-                                                          double& value, int32_t& ival, uint32_t& status) {
+                                                          double& value, int32_t& ival, uint32_t& status, uint32_t mask) {
   Parsed P;
   if (S.dbg & 1) { kh = r.off + len; value = 0.0; ival = (int32_t)len; status = 0; return BH_EV_OK; }
   uint32_t slow = 0;
-  if (!decode_straight(S, r, len, P)) {
+  if (!decode_straight(S, r, len, P, mask)) {
     Parsed Q;   // a separate object: P must not escape into the out-of-line slow path (it would live in local memory)
     if (!decode_slow(S, r, len, Q)) { kh = 0; value = 0.0; ival = 0; status = 0; return BH_EV_DROP_DECODE | kSlowDecode; }
     P = Q;
@@ -723,6 +731,7 @@ __device__ __forceinline__ void raw_warp_loop(const DevSchema& S, const uint8_t*
         if (lane < 18 && guess >= first && guess < total16) prefetch_l2(payload + guess);
       }
     }
+    const uint64_t aux = sink.preload(e, valid);        // e.g. the event's timestamp: in flight while the batch is parsed
     // A batch is one contiguous byte range, staged in the warp buffer and parsed from shared memory.
     // BIG = false (messages up to ~72 B expected): the batch is staged whole; a batch that does not fit
     // is parsed from global memory, every lane its own message.  BIG = true: a batch may also be staged
@@ -743,14 +752,16 @@ __device__ __forceinline__ void raw_warp_loop(const DevSchema& S, const uint8_t*
         const uint32_t bend = __shfl_sync(0xFFFFFFFFu, o1, min(q * g + g, cnt) - 1);
         stage_range(payload, A, min((bend + 15u) & ~15u, total16), wb, lane, S.dbg);
         __syncwarp();
-        if (valid && (!BIG || (lane / g) == q)) { SmemRd r{wb, o0 - A}; outcome = decode_and_check_smem(S, r, o1 - o0, kh, value, ival, status); }
+        const bool mine = valid && (!BIG || (lane / g) == q);
+        const uint32_t mask = __ballot_sync(0xFFFFFFFFu, mine);
+        if (mine) { SmemRd r{wb, o0 - A}; outcome = decode_and_check_smem(S, r, o1 - o0, kh, value, ival, status, mask); }
         __syncwarp();                               // the buffer is rewritten by the next part / batch
         if (!BIG) break;
       }
     } else if (valid && sane) {
       outcome = decode_and_check_gmem(S, payload + o0, o1 - o0, kh, value, ival, status);
     }
-    if (valid) sink.event(e, outcome, kh, value, ival, status);
+    if (valid) sink.event(e, outcome, kh, value, ival, status, aux);
   }
 }
 
@@ -761,12 +772,15 @@ struct AggSink {
   __device__ __forceinline__ void prefetch(uint32_t e2, uint32_t lane) const {
     if (S.has_window && ts && lane < 2) prefetch_l2(ts + e2 + lane * 16);
   }
-  __device__ __forceinline__ void event(uint32_t e, uint32_t outcome, uint64_t kh, double value, int32_t ival, uint32_t) {
+  __device__ __forceinline__ uint64_t preload(uint32_t e, bool valid) const {
+    return (valid && S.has_window && ts) ? ts[e] : 0ull;
+  }
+  __device__ __forceinline__ void event(uint32_t, uint32_t outcome, uint64_t kh, double value, int32_t ival, uint32_t, uint64_t ts_ms) {
     if (outcome & kSlowDecode) C.bump(C_SLOW);
     outcome &= 0xFFu;
     if (outcome != BH_EV_OK) { C.bump(outcome); return; }
     uint64_t win = 0;
-    if (S.has_window) win = div64(ts ? ts[e] : 0ull, S.wdiv);
+    if (S.has_window) win = div64(ts_ms, S.wdiv);
     aggregate_event<INTV>(S, T, M, kh, win, wbase, value, ival, C);
   }
 };
@@ -802,7 +816,8 @@ struct ColumnSink {
   const DevSchema& S;
   uint64_t* kh; double* val; int32_t* status; uint8_t* outcome;
   __device__ __forceinline__ void prefetch(uint32_t, uint32_t) const {}
-  __device__ __forceinline__ void event(uint32_t e, uint32_t oc, uint64_t k, double v, int32_t iv, uint32_t st) {
+  __device__ __forceinline__ uint64_t preload(uint32_t, bool) const { return 0ull; }
+  __device__ __forceinline__ void event(uint32_t e, uint32_t oc, uint64_t k, double v, int32_t iv, uint32_t st, uint64_t) {
     // integer value kinds: the fast path leaves `v` unset; (double)(int32) is the JS number
     oc &= 0xFFu;
     const bool have = oc != BH_EV_DROP_DECODE;
