@@ -173,16 +173,17 @@ struct LaneCounters {
 };
 
 // One event into the tables.  `wbase` is the CTA's first window minus one.
-// INTV: `iv` is the value; otherwise `v`.
+// INTV: `iv` is the value; otherwise `v`.  `mask` = the lanes that call it together.
 template <bool INTV>
 __device__ __forceinline__ void aggregate_event(const DevSchema& S, const DevTables& T, const SmemTable& M,
                                                 uint64_t kh, uint64_t win, uint64_t wbase, double v, int32_t iv,
-                                                LaneCounters& C) {
+                                                LaneCounters& C, uint32_t mask) {
   const uint32_t ops = S.ops;
   const uint64_t wr = win - wbase;
   int slot = -1;
   if (S.dbg & 16) slot = (int)((((uint32_t)kh ^ (uint32_t)(kh >> 32)) * 0x9E3779B1u) >> M.shift);
   else if (kh < kLockKey && wr < 255ull) slot = smem_find_or_insert(M, T, kh, (uint32_t)wr, win);
+  __syncwarp(mask);   // lanes leave the probe loop at different iterations: bring them back before the updates
   if (S.dbg & 8) { C.ok += (slot >= 0); return; }
   if (slot >= 0) {
     if (ops & BH_OP_HIST) {
@@ -761,7 +762,7 @@ __device__ __forceinline__ void raw_warp_loop(const DevSchema& S, const uint8_t*
     } else if (valid && sane) {
       outcome = decode_and_check_gmem(S, payload + o0, o1 - o0, kh, value, ival, status);
     }
-    if (valid) sink.event(e, outcome, kh, value, ival, status, aux);
+    sink.event(valid, e, outcome, kh, value, ival, status, aux);
   }
 }
 
@@ -775,13 +776,17 @@ struct AggSink {
   __device__ __forceinline__ uint64_t preload(uint32_t e, bool valid) const {
     return (valid && S.has_window && ts) ? ts[e] : 0ull;
   }
-  __device__ __forceinline__ void event(uint32_t, uint32_t outcome, uint64_t kh, double value, int32_t ival, uint32_t, uint64_t ts_ms) {
-    if (outcome & kSlowDecode) C.bump(C_SLOW);
+  // called by the whole (converged) warp; `valid` marks the lanes that carry an event
+  __device__ __forceinline__ void event(bool valid, uint32_t, uint32_t outcome, uint64_t kh, double value, int32_t ival, uint32_t, uint64_t ts_ms) {
+    if (valid && (outcome & kSlowDecode)) C.bump(C_SLOW);
     outcome &= 0xFFu;
-    if (outcome != BH_EV_OK) { C.bump(outcome); return; }
+    if (valid && outcome != BH_EV_OK) C.bump(outcome);
+    const bool ok = valid && outcome == BH_EV_OK;
+    const uint32_t mask = __ballot_sync(0xFFFFFFFFu, ok);
+    if (!ok) return;
     uint64_t win = 0;
     if (S.has_window) win = div64(ts_ms, S.wdiv);
-    aggregate_event<INTV>(S, T, M, kh, win, wbase, value, ival, C);
+    aggregate_event<INTV>(S, T, M, kh, win, wbase, value, ival, C, mask);
   }
 };
 
@@ -817,7 +822,8 @@ struct ColumnSink {
   uint64_t* kh; double* val; int32_t* status; uint8_t* outcome;
   __device__ __forceinline__ void prefetch(uint32_t, uint32_t) const {}
   __device__ __forceinline__ uint64_t preload(uint32_t, bool) const { return 0ull; }
-  __device__ __forceinline__ void event(uint32_t e, uint32_t oc, uint64_t k, double v, int32_t iv, uint32_t st, uint64_t) {
+  __device__ __forceinline__ void event(bool valid, uint32_t e, uint32_t oc, uint64_t k, double v, int32_t iv, uint32_t st, uint64_t) {
+    if (!valid) return;
     // integer value kinds: the fast path leaves `v` unset; (double)(int32) is the JS number
     oc &= 0xFFu;
     const bool have = oc != BH_EV_DROP_DECODE;
@@ -858,12 +864,22 @@ k_process_columns(const __grid_constant__ DevSchema S, const __grid_constant__ D
   uint64_t wbase = 0;
   if (cs < ce && S.has_window) { uint64_t w0 = div64(ts[cs], S.wdiv); wbase = w0 ? w0 - 1 : 0; }
   const bool need_value = (S.ops & (BH_OP_SUM | BH_OP_MIN | BH_OP_MAX | BH_OP_HIST)) != 0;
-  for (uint64_t i = cs + threadIdx.x; i < ce; i += blockDim.x) {
-    const uint64_t k = kh[i];
-    const double v = val ? val[i] : 0.0;
-    const uint64_t win = S.has_window ? div64(ts[i], S.wdiv) : 0ull;
-    if (need_value && v != v) { C.bump(C_NAN); continue; }
-    aggregate_event<false>(S, T, M, k, win, wbase, v, 0, C);
+  // one trip count per warp; the next iteration's three columns are loaded before this one is aggregated
+  const uint32_t lane = threadIdx.x & 31;
+  uint64_t base = cs + (threadIdx.x & ~31u);
+  uint64_t nk = 0, nt = 0; double nv = 0.0;
+  if (base + lane < ce) { nk = kh[base + lane]; nt = S.has_window ? ts[base + lane] : 0ull; nv = val ? val[base + lane] : 0.0; }
+  for (; base < ce; base += blockDim.x) {
+    const bool valid = base + lane < ce;
+    const uint64_t k = nk, t = nt; const double v = nv;
+    const uint64_t nxt = base + blockDim.x + lane;
+    if (nxt < ce) { nk = kh[nxt]; nt = S.has_window ? ts[nxt] : 0ull; nv = val ? val[nxt] : 0.0; }
+    const uint64_t win = valid && S.has_window ? div64(t, S.wdiv) : 0ull;
+    const bool nan = need_value && v != v;
+    if (valid && nan) C.bump(C_NAN);
+    const bool ok = valid && !nan;
+    const uint32_t mask = __ballot_sync(0xFFFFFFFFu, ok);
+    if (ok) aggregate_event<false>(S, T, M, k, win, wbase, v, 0, C, mask);
   }
   __syncthreads();
   smem_table_flush<false>(S, T, M, wbase);
