@@ -119,7 +119,6 @@ int build_schema(const bh_config& cfg, DevSchema& S) {
   S.big_messages = cfg.message_bytes_hint > 72;
   S.n_parts = parts;
   S.mode = cfg.mode;
-  if (const char* d = getenv("BH_DEBUG_SKIP")) S.dbg = (uint32_t)atoi(d);
   if (cfg.mode == BH_MODE_REFERENCE) {
     if (!have_status) return fail(nullptr, BH_ERR_INVALID, "REFERENCE mode needs a field with BH_R_STATUS");
     S.status_part = 1;

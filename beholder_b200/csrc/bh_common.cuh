@@ -113,7 +113,6 @@ struct DevSchema {
   uint32_t fast_value_f64;   // ... and it is a double
   uint32_t tag_key0, tag_status, tag_value;   // their canonical one-byte tags (0xFFFFFFFF = none)
   uint32_t big_messages;     // messages above ~72 B expected: kernels that stage a batch in parts
-  uint32_t dbg;              // BH_DEBUG_SKIP (timing experiments): 1 no parse, 2 no hash, 4 no staging
   Div64 wdiv;
 };
 

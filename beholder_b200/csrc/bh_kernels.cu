@@ -181,10 +181,8 @@ __device__ __forceinline__ void aggregate_event(const DevSchema& S, const DevTab
   const uint32_t ops = S.ops;
   const uint64_t wr = win - wbase;
   int slot = -1;
-  if (S.dbg & 16) slot = (int)((((uint32_t)kh ^ (uint32_t)(kh >> 32)) * 0x9E3779B1u) >> M.shift);
-  else if (kh < kLockKey && wr < 255ull) slot = smem_find_or_insert(M, T, kh, (uint32_t)wr, win);
+  if (kh < kLockKey && wr < 255ull) slot = smem_find_or_insert(M, T, kh, (uint32_t)wr, win);
   __syncwarp(mask);   // lanes leave the probe loop at different iterations: bring them back before the updates
-  if (S.dbg & 8) { C.ok += (slot >= 0); return; }
   if (slot >= 0) {
     if (ops & BH_OP_HIST) {
       if (INTV) v = (double)iv;
@@ -642,7 +640,6 @@ __device__ __noinline__ bool decode_slow(const DevSchema& S, const SmemRd& r, ui
 __device__ __forceinline__ uint32_t decode_and_check_smem(const DevSchema& S, const SmemRd& r, uint32_t len, uint64_t& kh,
                                                           double& value, int32_t& ival, uint32_t& status, uint32_t mask) {
   Parsed P;
-  if (S.dbg & 1) { kh = r.off + len; value = 0.0; ival = (int32_t)len; status = 0; return BH_EV_OK; }
   uint32_t slow = 0;
   if (!decode_straight(S, r, len, P, mask)) {
     Parsed Q;   // a separate object: P must not escape into the out-of-line slow path (it would live in local memory)
@@ -650,7 +647,7 @@ __device__ __forceinline__ uint32_t decode_and_check_smem(const DevSchema& S, co
     P = Q;
     slow = kSlowDecode;
   }
-  kh = (S.dbg & 2) ? (uint64_t)P.ppos[0] * 0x9E3779B97F4A7C15ull + P.status : event_key_hash_smem(S, r, P);
+  kh = event_key_hash_smem(S, r, P);
   return finish_event(S, P, value, ival, status) | slow;
 }
 
@@ -682,13 +679,13 @@ __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefe
 
 // coalesced copy of payload[A, B) (both multiples of 16) into the skewed warp buffer
 __device__ __forceinline__ void stage_range(const uint8_t* __restrict__ payload, uint32_t A, uint32_t B, uint32_t wb,
-                                            uint32_t lane, uint32_t dbg) {
+                                            uint32_t lane) {
   const uint4* src = reinterpret_cast<const uint4*>(payload + A);
   const uint32_t nvec = (B - A) >> 4;
   uint4 v[kWarpChunks];
 #pragma unroll
   for (uint32_t k = 0; k < kWarpChunks; k++)
-    if (lane + 32 * k < nvec && !(dbg & 4)) v[k] = ldg_stream(src + lane + 32 * k);
+    if (lane + 32 * k < nvec) v[k] = ldg_stream(src + lane + 32 * k);
 #pragma unroll
   for (uint32_t k = 0; k < kWarpChunks; k++) {
     const uint32_t i = lane + 32 * k;
@@ -751,7 +748,7 @@ __device__ __forceinline__ void raw_warp_loop(const DevSchema& S, const uint8_t*
       for (uint32_t q = 0; q * g < cnt; q++) {
         const uint32_t A = __shfl_sync(0xFFFFFFFFu, o0, q * g) & ~15u;
         const uint32_t bend = __shfl_sync(0xFFFFFFFFu, o1, min(q * g + g, cnt) - 1);
-        stage_range(payload, A, min((bend + 15u) & ~15u, total16), wb, lane, S.dbg);
+        stage_range(payload, A, min((bend + 15u) & ~15u, total16), wb, lane);
         __syncwarp();
         const bool mine = valid && (!BIG || (lane / g) == q);
         const uint32_t mask = __ballot_sync(0xFFFFFFFFu, mine);
