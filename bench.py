@@ -336,6 +336,15 @@ def main():
             torch.from_numpy(hp).copy_(p); torch.from_numpy(ho.view(np.int32)).copy_(o); torch.from_numpy(ht.view(np.int64)).copy_(t_)
             pins.append((pb, ob, tb, hp, ho, ht, n, total))
         torch.cuda.synchronize()
+        # the ingest roofline: plain pinned-host -> device copies of the first slab, best of 5 (CUDA events)
+        src = torch.from_numpy(pins[0][3]); dst = torch.empty_like(slabs[0][0])
+        best = 0.0
+        for _ in range(5):
+            c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            c0.record(); dst.copy_(src, non_blocking=True); c1.record(); torch.cuda.synchronize()
+            best = max(best, src.numel() / (c0.elapsed_time(c1) * 1e-3) / 1e9)
+        pcie_peak = best
+        del dst
         ing = mk()
         h2d = sum(total + (n + 1) * 4 + n * 8 for *_, n, total in pins)
 
@@ -367,14 +376,17 @@ def main():
                "d2h_bytes_per_step": rows * 48 + 8 * 40, "steps": e2e_steps,
                "path": "bh_push_batch_pinned -> (pinned host -> HBM in 64 MiB ring slabs on 2 copy streams) -> "
                        "k_process_raw -> bh_flush -> bh_snapshot of every window",
-               "pcie_gbs": world * h2d * e2e_steps / dt / 1e9}
+               "pcie_gbs": world * h2d * e2e_steps / dt / 1e9,
+               "pcie_peak_gbs_per_gpu": pcie_peak, "pcie_frac": (h2d * e2e_steps / dt / 1e9) / pcie_peak,
+               "bound": "PCIe H2D ingest (measured pinned-copy peak per GPU in pcie_peak_gbs_per_gpu)"}
         ing.close()
         for pb, ob, tb, *_ in pins:
             pb.free(); ob.free(); tb.free()
 
     if rank == 0:
         peak, peak_src = peaks()
-        launches_per_step = SLABS + (exch.kernel_launches_per_close + 5 if exch else 0)
+        # our kernels per step: one fused launch per slab; with N > 1 also export (count, prefix, scatter) + merge
+        launches_per_step = SLABS + (exch.kernel_launches_per_close if exch else 0)
         per_launch_s = kernel_ms * 1e-3 / (args.steps * SLABS)
         per_launch_bytes = sum(total + (n + 1) * 4 + n * 8 for *_, n, total in slabs) / SLABS
         achieved = per_launch_bytes / per_launch_s / 1e9
