@@ -675,6 +675,7 @@ __device__ __forceinline__ uint4 ldg_stream(const uint4* p) {
   asm("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
   return v;
 }
+constexpr uint32_t kPrefetchAhead = 4;   // batches ahead whose cache lines are pulled into L2
 __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" :: "l"(p)); }
 
 // coalesced copy of payload[A, B) (both multiples of 16) into the skewed warp buffer
@@ -719,13 +720,13 @@ __device__ __forceinline__ void raw_warp_loop(const DevSchema& S, const uint8_t*
       const uint32_t en = e + step;
       n0 = 0; n1 = 0;
       if (en < ce) { n0 = offsets[en]; n1 = offsets[en + 1]; }
-      const uint32_t e2 = e0 + 2 * step;
+      const uint32_t e2 = e0 + kPrefetchAhead * step;
       if (e2 < ce) {
         if (lane == 0) prefetch_l2(offsets + e2);
         sink.prefetch(e2, lane);
-        // payload two batches ahead: its byte range is not known yet; extrapolate from this batch's
+        // payload a few batches ahead: its byte range is not known yet; extrapolate from this batch's
         const uint32_t first = __shfl_sync(0xFFFFFFFFu, o0, 0), last = __shfl_sync(0xFFFFFFFFu, o1, 31);
-        const uint32_t guess = first + 2u * (last - first) * nwarps + lane * 128u;
+        const uint32_t guess = first + kPrefetchAhead * (last - first) * nwarps + lane * 128u;
         if (lane < 18 && guess >= first && guess < total16) prefetch_l2(payload + guess);
       }
     }

@@ -7,7 +7,7 @@ import beholder_b200 as bh
 from beholder_b200 import _lib as L
 from beholder_b200.synth import SynthSpec, generate_host, generate_device, columns_device, zipf_cdf
 from oracle import oracle as O
-from helpers import ALL_OPS, SEED, assert_records_equal, load_json, pack
+from helpers import ALL_OPS, SEED, assert_records_equal, load_json, pack, sort_records
 
 pytestmark = pytest.mark.gpu
 KEY = ("mediaId", "status")
@@ -213,3 +213,30 @@ def test_full_size_properties_c2():
     assert len(np.unique(o1["window_id"])) >= 20 and len(np.unique(o1["key_hash"])) == 1000
     # integer progress 0..100: sums are integers and exactly representable -> must be exact
     assert np.array_equal(o1["sum"], np.round(o1["sum"])) and (o1["min"] >= 0).all() and (o1["max"] <= 100).all()
+
+
+def test_integer_table_carries_and_negative_values():
+    """int32 `progress` over the whole range: the shared table keeps the sum in two 32-bit words
+    (native atomics, carry / sign handled by hand) and min/max as int32; multi-byte and 10-byte varints
+    take the decoder's slow tiers.  Everything must equal the oracle exactly (sums are integers < 2^53)."""
+    rng = np.random.default_rng(5)
+    schema = bh.telemetry_progress()
+    n = 60_000
+    vals = np.concatenate([rng.integers(-2**31, 2**31, n // 2), rng.integers(-3, 130, n // 4),
+                           np.full(n // 8, 2**31 - 1), np.full(n // 8, -2**31)]).astype(np.int64)
+    rng.shuffle(vals)
+    payloads = [bh.encode(schema, mediaId="m%d" % (i % 7), status=int(i % 6), progress=int(v)) for i, v in enumerate(vals)]
+    slab, off = pack(payloads)
+    ts = (np.uint64(1_700_000_000_000) + (np.arange(len(payloads), dtype=np.uint64) // np.uint64(3)))
+    with bh.Aggregator(schema, mode=L.MODE_WINDOWED, key=KEY, ops=ALL_OPS, table_capacity=256) as g:
+        g.push_batch(slab, off, ts)
+        g.flush()
+        got = g.snapshot_all()
+        k = g.counters()
+    a = O.Agg(schema.with_roles(key=KEY), ALL_OPS, 10_000, SEED)
+    a.push_raw(slab, off, ts)
+    want = a.snapshot()
+    assert_records_equal(got, want, ALL_OPS)
+    gs, ws = sort_records(got), sort_records(want)
+    assert np.array_equal(gs["sum"], ws["sum"])            # exact, not just within tolerance
+    assert k["slow_decodes"] > n // 2 and k["events_ok"] == len(payloads)
