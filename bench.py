@@ -260,6 +260,9 @@ def main():
         raise SystemExit("bench.py needs a CUDA device: beholder_b200 has no CPU path")
     torch.cuda.set_device(local_rank)
     if world > 1:
+        # keep stdout to the one JSON line: NCCL prints its version banner there at NCCL_DEBUG=VERSION
+        if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
+            os.environ["NCCL_DEBUG"] = "WARN"
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     events = args.events
     ops = L.OP_COUNT | L.OP_SUM | L.OP_MIN | L.OP_MAX
