@@ -70,13 +70,27 @@ __device__ __forceinline__ void g_update(const DevTables& T, uint32_t ops, uint6
 //         ATOMS.CAST.SPIN loops are used.  37 B per slot.
 // =========================================================================================
 struct SmemTable {
-  unsigned long long* key;
-  uint32_t* cnt;
-  uint32_t* gslot;          // HBM slot of the entry; only when histograms are on (else nullptr)
-  uint8_t* wrel;            // window - wbase
-  void* va; void* vb; void* vc; void* vd;   // INTV: sum_lo u32, sum_hi i32, min i32, max i32 | F64: sum, -, min_inv, max_ord
+  // Only the base and the slot count are kept (3 registers); the column arrays are found from them at
+  // each use: key u64[ns] | INTV: sum_lo u32, sum_hi i32, min i32, max i32 / F64: sum f64, min_inv u64,
+  // max_ord u64 | cnt u32[ns] | gslot u32[ns] (histograms only) | wrel u8[ns]
+  uint8_t* base;
   uint32_t ns;              // power of two
   uint32_t shift;           // 32 - log2(ns)
+  uint32_t hist;            // gslot column present
+  __device__ __forceinline__ unsigned long long* key() const { return (unsigned long long*)base; }
+  template <bool INTV> __device__ __forceinline__ uint8_t* vals() const { return base + (size_t)ns * 8; }
+  template <bool INTV> __device__ __forceinline__ uint32_t* cnt() const { return (uint32_t*)(base + (size_t)ns * (INTV ? 24 : 32)); }
+  template <bool INTV> __device__ __forceinline__ uint32_t* gslot() const { return hist ? (uint32_t*)(base + (size_t)ns * (INTV ? 28 : 36)) : nullptr; }
+  template <bool INTV> __device__ __forceinline__ uint8_t* wrel() const { return base + (size_t)ns * ((INTV ? 28 : 36) + (hist ? 4 : 0)); }
+  // INTV value columns
+  __device__ __forceinline__ uint32_t* sum_lo() const { return (uint32_t*)(base + (size_t)ns * 8); }
+  __device__ __forceinline__ int32_t* sum_hi() const { return (int32_t*)(base + (size_t)ns * 12); }
+  __device__ __forceinline__ int32_t* imin() const { return (int32_t*)(base + (size_t)ns * 16); }
+  __device__ __forceinline__ int32_t* imax() const { return (int32_t*)(base + (size_t)ns * 20); }
+  // F64 value columns
+  __device__ __forceinline__ double* fsum() const { return (double*)(base + (size_t)ns * 8); }
+  __device__ __forceinline__ unsigned long long* fmin_inv() const { return (unsigned long long*)(base + (size_t)ns * 16); }
+  __device__ __forceinline__ unsigned long long* fmax_ord() const { return (unsigned long long*)(base + (size_t)ns * 24); }
 };
 constexpr int kSmemProbes = 16;
 constexpr uint32_t kWrelUnset = 0xFFu;   // window byte of a claimed slot that its owner has not filled in yet
@@ -87,14 +101,7 @@ __host__ __device__ constexpr uint32_t smem_slot_bytes(bool intv, bool hist) {
 template <bool INTV>
 __device__ __forceinline__ SmemTable smem_table_carve(uint8_t* base, uint32_t ns, bool hist) {
   SmemTable M;
-  M.key = (unsigned long long*)base;
-  uint8_t* p = base + (size_t)ns * 8;
-  if (INTV) { M.va = p; M.vb = p + (size_t)ns * 4; M.vc = p + (size_t)ns * 8; M.vd = p + (size_t)ns * 12; p += (size_t)ns * 16; }
-  else { M.va = p; M.vb = nullptr; M.vc = p + (size_t)ns * 8; M.vd = p + (size_t)ns * 16; p += (size_t)ns * 24; }
-  M.cnt = (uint32_t*)p; p += (size_t)ns * 4;
-  M.gslot = hist ? (uint32_t*)p : nullptr; if (hist) p += (size_t)ns * 4;
-  M.wrel = p;
-  M.ns = ns;
+  M.base = base; M.ns = ns; M.hist = hist;
   M.shift = 32u - (31u - (uint32_t)__clz((int)ns));
   return M;
 }
@@ -102,14 +109,10 @@ __device__ __forceinline__ SmemTable smem_table_carve(uint8_t* base, uint32_t ns
 template <bool INTV>
 __device__ __forceinline__ void smem_table_clear(const SmemTable& M) {
   for (uint32_t i = threadIdx.x; i < M.ns; i += blockDim.x) {
-    M.key[i] = kEmptyKey; M.cnt[i] = 0; M.wrel[i] = (uint8_t)kWrelUnset;
-    if (M.gslot) M.gslot[i] = 0;
-    if (INTV) {
-      ((uint32_t*)M.va)[i] = 0; ((int32_t*)M.vb)[i] = 0;
-      ((int32_t*)M.vc)[i] = 0x7FFFFFFF; ((int32_t*)M.vd)[i] = (int32_t)0x80000000;
-    } else {
-      ((double*)M.va)[i] = 0.0; ((unsigned long long*)M.vc)[i] = 0; ((unsigned long long*)M.vd)[i] = 0;
-    }
+    M.key()[i] = kEmptyKey; M.cnt<INTV>()[i] = 0; M.wrel<INTV>()[i] = (uint8_t)kWrelUnset;
+    if (M.hist) M.gslot<INTV>()[i] = 0;
+    if (INTV) { M.sum_lo()[i] = 0; M.sum_hi()[i] = 0; M.imin()[i] = 0x7FFFFFFF; M.imax()[i] = (int32_t)0x80000000; }
+    else { M.fsum()[i] = 0.0; M.fmin_inv()[i] = 0; M.fmax_ord()[i] = 0; }
   }
 }
 
@@ -121,17 +124,18 @@ __device__ __forceinline__ void smem_table_clear(const SmemTable& M) {
 // Slow half: claim a slot (or find the key someone else is inserting right now), starting at `slot`.
 // Kept out of line: the CAS and the wait loop make the compiler add yields and convergence barriers
 // that must not sit in the hot look-up loop.
-__device__ __noinline__ int smem_insert(const SmemTable& M, const DevTables& T, uint64_t kh, uint32_t wrel,
+template <bool INTV>
+__device__ __noinline__ int smem_insert(const SmemTable M, const DevTables& T, uint64_t kh, uint32_t wrel,
                                         uint64_t win, uint32_t slot, int probes_left) {
-  volatile unsigned long long* vkey = M.key;
-  volatile uint8_t* vwrel = M.wrel;
+  volatile unsigned long long* vkey = M.key();
+  volatile uint8_t* vwrel = M.wrel<INTV>();
 #pragma unroll 1
   for (int p = 0; p < probes_left; p++) {
     unsigned long long k = vkey[slot];
     if (k == kEmptyKey) {
-      k = atomicCAS(&M.key[slot], (unsigned long long)kEmptyKey, (unsigned long long)kh);
+      k = atomicCAS(&M.key()[slot], (unsigned long long)kEmptyKey, (unsigned long long)kh);
       if (k == kEmptyKey) {     // claimed
-        if (M.gslot) { uint32_t r; M.gslot[slot] = g_find_or_insert(T, win, kh, &r); __threadfence_block(); }
+        if (M.hist) { uint32_t r; M.gslot<INTV>()[slot] = g_find_or_insert(T, win, kh, &r); __threadfence_block(); }
         vwrel[slot] = (uint8_t)wrel;
         return (int)slot;
       }
@@ -147,6 +151,7 @@ __device__ __noinline__ int smem_insert(const SmemTable& M, const DevTables& T, 
 }
 
 // Hot half: read-only look-up (plain shared loads, no atomics, no waiting).
+template <bool INTV>
 __device__ __forceinline__ int smem_find_or_insert(const SmemTable& M, const DevTables& T, uint64_t kh,
                                                    uint32_t wrel, uint64_t win) {
   uint32_t x = (uint32_t)kh ^ (uint32_t)(kh >> 32) ^ (wrel * 0x85EBCA6Bu);
@@ -154,14 +159,14 @@ __device__ __forceinline__ int smem_find_or_insert(const SmemTable& M, const Dev
   int p = 0;
 #pragma unroll 1
   for (; p < kSmemProbes; p++) {
-    const unsigned long long k = M.key[slot];
-    const uint32_t w = M.wrel[slot];
+    const unsigned long long k = M.key()[slot];
+    const uint32_t w = M.wrel<INTV>()[slot];
     if (k == kh && w == wrel) return (int)slot;
     if (k == kEmptyKey || (k == kh && w == kWrelUnset)) break;   // not here (yet): go and insert / wait
     slot = (slot + 1) & (M.ns - 1);
   }
   if (p == kSmemProbes) return -1;
-  return smem_insert(M, T, kh, wrel, win, slot, kSmemProbes - p);
+  return smem_insert<INTV>(M, T, kh, wrel, win, slot, kSmemProbes - p);
 }
 
 // Outcome counters of a CTA.  Only the count of aggregated events lives in a register; drops, spills
@@ -181,31 +186,31 @@ __device__ __forceinline__ void aggregate_event(const DevSchema& S, const DevTab
   const uint32_t ops = S.ops;
   const uint64_t wr = win - wbase;
   int slot = -1;
-  if (kh < kLockKey && wr < 255ull) slot = smem_find_or_insert(M, T, kh, (uint32_t)wr, win);
+  if (kh < kLockKey && wr < 255ull) slot = smem_find_or_insert<INTV>(M, T, kh, (uint32_t)wr, win);
   __syncwarp(mask);   // lanes leave the probe loop at different iterations: bring them back before the updates
   if (slot >= 0) {
     if (ops & BH_OP_HIST) {
       if (INTV) v = (double)iv;
-      uint32_t gs = M.gslot[slot];
+      uint32_t gs = M.gslot<INTV>()[slot];
       if (gs >= kGslotWindow) { C.bump(gs == kGslotFull ? C_TABLE_FULL : C_WINDOW); return; }
       uint64_t gi = (uint64_t)((uint32_t)win & (T.ring - 1)) * T.stride + gs;
       atomicAdd(&T.hist[gi * T.hist_buckets + hist_bucket((uint64_t)__double_as_longlong(v), T.hist_buckets, S.hist_e0)], 1u);
     }
-    atomicAdd(&M.cnt[slot], 1u);
+    atomicAdd(&M.cnt<INTV>()[slot], 1u);
     if (INTV) {
       if (ops & BH_OP_SUM) {
         const uint32_t add = (uint32_t)iv;
-        const uint32_t old = atomicAdd((uint32_t*)M.va + slot, add);
+        const uint32_t old = atomicAdd(M.sum_lo() + slot, add);
         const int32_t hi = (iv >> 31) + (int32_t)(old + add < old);   // sign extension + carry
-        if (hi) atomicAdd((int32_t*)M.vb + slot, hi);
+        if (hi) atomicAdd(M.sum_hi() + slot, hi);
       }
-      if (ops & BH_OP_MIN) atomicMin((int32_t*)M.vc + slot, iv);
-      if (ops & BH_OP_MAX) atomicMax((int32_t*)M.vd + slot, iv);
+      if (ops & BH_OP_MIN) atomicMin(M.imin() + slot, iv);
+      if (ops & BH_OP_MAX) atomicMax(M.imax() + slot, iv);
     } else {
       const uint64_t ord = f64_order((uint64_t)__double_as_longlong(v));
-      if (ops & BH_OP_SUM) atomicAdd((double*)M.va + slot, v);
-      if (ops & BH_OP_MIN) atomicMax((unsigned long long*)M.vc + slot, (unsigned long long)~ord);
-      if (ops & BH_OP_MAX) atomicMax((unsigned long long*)M.vd + slot, (unsigned long long)ord);
+      if (ops & BH_OP_SUM) atomicAdd(M.fsum() + slot, v);
+      if (ops & BH_OP_MIN) atomicMax(M.fmin_inv() + slot, (unsigned long long)~ord);
+      if (ops & BH_OP_MAX) atomicMax(M.fmax_ord() + slot, (unsigned long long)ord);
     }
     C.ok++;
     return;
@@ -232,14 +237,14 @@ __device__ __forceinline__ void smem_table_flush(const DevSchema& S, const DevTa
   const uint32_t rot = (blockIdx.x * 0x9E3779B1u) >> M.shift;
   for (uint32_t j = threadIdx.x; j < M.ns; j += blockDim.x) {
     const uint32_t i = (j + rot) & (M.ns - 1);
-    unsigned long long k = M.key[i];
-    uint32_t c = M.cnt[i];
+    unsigned long long k = M.key()[i];
+    uint32_t c = M.cnt<INTV>()[i];
     if (k == kEmptyKey || c == 0) continue;
-    uint64_t win = wbase + M.wrel[i];
+    uint64_t win = wbase + M.wrel<INTV>()[i];
     uint32_t r = (uint32_t)win & (T.ring - 1);
-    uint32_t gs = M.gslot ? M.gslot[i] : g_find_or_insert(T, win, k, &r);
+    uint32_t gs = M.hist ? M.gslot<INTV>()[i] : g_find_or_insert(T, win, k, &r);
     if (gs >= kGslotWindow) {
-      if (!M.gslot) {   // (with histograms on, the event was already refused when it arrived)
+      if (!M.hist) {   // (with histograms on, the event was already refused when it arrived)
         atomicAdd(&T.counters[gs == kGslotFull ? C_TABLE_FULL : C_WINDOW], (unsigned long long)c);
         atomicAdd(&T.counters[C_OK], 0ull - (unsigned long long)c);
       }
@@ -247,12 +252,12 @@ __device__ __forceinline__ void smem_table_flush(const DevSchema& S, const DevTa
     }
     double sum; unsigned long long mn_inv, mx_ord;
     if (INTV) {
-      long long s64 = (long long)(((unsigned long long)(uint32_t)((int32_t*)M.vb)[i] << 32) | ((uint32_t*)M.va)[i]);
+      long long s64 = (long long)(((unsigned long long)(uint32_t)M.sum_hi()[i] << 32) | M.sum_lo()[i]);
       sum = (double)s64;
-      mn_inv = ~f64_order((uint64_t)__double_as_longlong((double)((int32_t*)M.vc)[i]));
-      mx_ord = f64_order((uint64_t)__double_as_longlong((double)((int32_t*)M.vd)[i]));
+      mn_inv = ~f64_order((uint64_t)__double_as_longlong((double)M.imin()[i]));
+      mx_ord = f64_order((uint64_t)__double_as_longlong((double)M.imax()[i]));
     } else {
-      sum = ((double*)M.va)[i]; mn_inv = ((unsigned long long*)M.vc)[i]; mx_ord = ((unsigned long long*)M.vd)[i];
+      sum = M.fsum()[i]; mn_inv = M.fmin_inv()[i]; mx_ord = M.fmax_ord()[i];
     }
     g_update(T, S.ops, (uint64_t)r * T.stride + gs, c, sum, mn_inv, mx_ord);
   }
