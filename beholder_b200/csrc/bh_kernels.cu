@@ -69,28 +69,32 @@ __device__ __forceinline__ void g_update(const DevTables& T, uint32_t ops, uint6
 //         order-preserving u64; shared memory has no native 64-bit add/max, the compiler's
 //         ATOMS.CAST.SPIN loops are used.  37 B per slot.
 // =========================================================================================
+// Dynamic shared memory of the aggregating kernels and their 8 outcome counters, named at file scope so
+// that every access is a plain shared-space access (32-bit address, no generic pointer kept in registers).
+extern __shared__ __align__(16) uint8_t g_smem[];
+__shared__ uint32_t g_cnt[8];
+
 struct SmemTable {
-  // Only the base and the slot count are kept (3 registers); the column arrays are found from them at
+  // Only the slot count is kept; the column arrays are found from it and the shared base at
   // each use: key u64[ns] | INTV: sum_lo u32, sum_hi i32, min i32, max i32 / F64: sum f64, min_inv u64,
   // max_ord u64 | cnt u32[ns] | gslot u32[ns] (histograms only) | wrel u8[ns]
-  uint8_t* base;
   uint32_t ns;              // power of two
   uint32_t shift;           // 32 - log2(ns)
   uint32_t hist;            // gslot column present
-  __device__ __forceinline__ unsigned long long* key() const { return (unsigned long long*)base; }
-  template <bool INTV> __device__ __forceinline__ uint8_t* vals() const { return base + (size_t)ns * 8; }
-  template <bool INTV> __device__ __forceinline__ uint32_t* cnt() const { return (uint32_t*)(base + (size_t)ns * (INTV ? 24 : 32)); }
-  template <bool INTV> __device__ __forceinline__ uint32_t* gslot() const { return hist ? (uint32_t*)(base + (size_t)ns * (INTV ? 28 : 36)) : nullptr; }
-  template <bool INTV> __device__ __forceinline__ uint8_t* wrel() const { return base + (size_t)ns * ((INTV ? 28 : 36) + (hist ? 4 : 0)); }
+  __device__ __forceinline__ unsigned long long* key() const { return (unsigned long long*)g_smem; }
+  template <bool INTV> __device__ __forceinline__ uint8_t* vals() const { return g_smem + (size_t)ns * 8; }
+  template <bool INTV> __device__ __forceinline__ uint32_t* cnt() const { return (uint32_t*)(g_smem + (size_t)ns * (INTV ? 24 : 32)); }
+  template <bool INTV> __device__ __forceinline__ uint32_t* gslot() const { return hist ? (uint32_t*)(g_smem + (size_t)ns * (INTV ? 28 : 36)) : nullptr; }
+  template <bool INTV> __device__ __forceinline__ uint8_t* wrel() const { return g_smem + (size_t)ns * ((INTV ? 28 : 36) + (hist ? 4 : 0)); }
   // INTV value columns
-  __device__ __forceinline__ uint32_t* sum_lo() const { return (uint32_t*)(base + (size_t)ns * 8); }
-  __device__ __forceinline__ int32_t* sum_hi() const { return (int32_t*)(base + (size_t)ns * 12); }
-  __device__ __forceinline__ int32_t* imin() const { return (int32_t*)(base + (size_t)ns * 16); }
-  __device__ __forceinline__ int32_t* imax() const { return (int32_t*)(base + (size_t)ns * 20); }
+  __device__ __forceinline__ uint32_t* sum_lo() const { return (uint32_t*)(g_smem + (size_t)ns * 8); }
+  __device__ __forceinline__ int32_t* sum_hi() const { return (int32_t*)(g_smem + (size_t)ns * 12); }
+  __device__ __forceinline__ int32_t* imin() const { return (int32_t*)(g_smem + (size_t)ns * 16); }
+  __device__ __forceinline__ int32_t* imax() const { return (int32_t*)(g_smem + (size_t)ns * 20); }
   // F64 value columns
-  __device__ __forceinline__ double* fsum() const { return (double*)(base + (size_t)ns * 8); }
-  __device__ __forceinline__ unsigned long long* fmin_inv() const { return (unsigned long long*)(base + (size_t)ns * 16); }
-  __device__ __forceinline__ unsigned long long* fmax_ord() const { return (unsigned long long*)(base + (size_t)ns * 24); }
+  __device__ __forceinline__ double* fsum() const { return (double*)(g_smem + (size_t)ns * 8); }
+  __device__ __forceinline__ unsigned long long* fmin_inv() const { return (unsigned long long*)(g_smem + (size_t)ns * 16); }
+  __device__ __forceinline__ unsigned long long* fmax_ord() const { return (unsigned long long*)(g_smem + (size_t)ns * 24); }
 };
 constexpr int kSmemProbes = 16;
 constexpr uint32_t kWrelUnset = 0xFFu;   // window byte of a claimed slot that its owner has not filled in yet
@@ -99,9 +103,9 @@ __host__ __device__ constexpr uint32_t smem_slot_bytes(bool intv, bool hist) {
 }
 
 template <bool INTV>
-__device__ __forceinline__ SmemTable smem_table_carve(uint8_t* base, uint32_t ns, bool hist) {
+__device__ __forceinline__ SmemTable smem_table_carve(uint32_t ns, bool hist) {
   SmemTable M;
-  M.base = base; M.ns = ns; M.hist = hist;
+  M.ns = ns; M.hist = hist;
   M.shift = 32u - (31u - (uint32_t)__clz((int)ns));
   return M;
 }
@@ -173,8 +177,7 @@ __device__ __forceinline__ int smem_find_or_insert(const SmemTable& M, const Dev
 // and slow decodes are rare and go straight to a shared-memory array (keeps 7 registers out of the loop).
 struct LaneCounters {
   uint32_t ok;
-  uint32_t* s;     // shared: u32[8], zeroed by the kernel
-  __device__ __forceinline__ void bump(uint32_t which) { atomicAdd(&s[which], 1u); }
+  __device__ __forceinline__ void bump(uint32_t which) { atomicAdd(&g_cnt[which], 1u); }   // g_cnt: zeroed by the kernel
 };
 
 // One event into the tables.  `wbase` is the CTA's first window minus one.
@@ -263,11 +266,11 @@ __device__ __forceinline__ void smem_table_flush(const DevSchema& S, const DevTa
   }
 }
 
-__device__ __forceinline__ void counters_flush(const DevTables& T, LaneCounters& C, uint32_t* s_cnt /*[8]*/) {
+__device__ __forceinline__ void counters_flush(const DevTables& T, LaneCounters& C) {
   uint32_t v = __reduce_add_sync(0xFFFFFFFFu, C.ok);
-  if ((threadIdx.x & 31) == 0 && v) atomicAdd(&s_cnt[C_OK], v);
+  if ((threadIdx.x & 31) == 0 && v) atomicAdd(&g_cnt[C_OK], v);
   __syncthreads();
-  if (threadIdx.x < 8 && s_cnt[threadIdx.x]) atomicAdd(&T.counters[threadIdx.x], (unsigned long long)s_cnt[threadIdx.x]);
+  if (threadIdx.x < 8 && g_cnt[threadIdx.x]) atomicAdd(&T.counters[threadIdx.x], (unsigned long long)g_cnt[threadIdx.x]);
 }
 
 // shared-memory access by 32-bit shared-window address, for the staged payload bytes
@@ -798,17 +801,15 @@ __global__ void __launch_bounds__(INTV ? kRawThreads : kRawThreadsF64, 1)
 k_process_raw(const __grid_constant__ DevSchema S, const __grid_constant__ DevTables T,
               const uint8_t* __restrict__ payload, const uint32_t* __restrict__ offsets,
               const uint64_t* __restrict__ ts, uint32_t n, uint32_t chunk, uint32_t ns) {
-  extern __shared__ __align__(16) uint8_t smem[];
-  __shared__ uint32_t s_cnt[8];
   const bool hist = (S.ops & BH_OP_HIST) != 0;
-  const SmemTable M = smem_table_carve<INTV>(smem, ns, hist);
-  const uint32_t wb = (uint32_t)__cvta_generic_to_shared(smem) + ((ns * smem_slot_bytes(INTV, hist) + 15u) & ~15u) +
+  const SmemTable M = smem_table_carve<INTV>(ns, hist);
+  const uint32_t wb = (uint32_t)__cvta_generic_to_shared(g_smem) + ((ns * smem_slot_bytes(INTV, hist) + 15u) & ~15u) +
                       (threadIdx.x >> 5) * kWarpBufAlloc;
   smem_table_clear<INTV>(M);
-  if (threadIdx.x < 8) s_cnt[threadIdx.x] = 0;
+  if (threadIdx.x < 8) g_cnt[threadIdx.x] = 0;
   __syncthreads();
   const uint32_t cs = min(n, blockIdx.x * chunk), ce = min(n, cs + chunk);
-  LaneCounters C{0u, s_cnt};
+  LaneCounters C{0u};
   uint64_t wbase = 0;
   if (cs < ce) {
     if (S.has_window) { uint64_t w0 = div64(ts ? ts[cs] : 0ull, S.wdiv); wbase = w0 ? w0 - 1 : 0; }
@@ -817,7 +818,7 @@ k_process_raw(const __grid_constant__ DevSchema S, const __grid_constant__ DevTa
   }
   __syncthreads();
   smem_table_flush<INTV>(S, T, M, wbase);
-  counters_flush(T, C, s_cnt);
+  counters_flush(T, C);
 }
 
 struct ColumnSink {
@@ -839,8 +840,7 @@ __global__ void __launch_bounds__(kRawThreads, 1)
 k_decode(const __grid_constant__ DevSchema S, const uint8_t* __restrict__ payload,
          const uint32_t* __restrict__ offsets, uint32_t n, uint32_t chunk, uint64_t* kh, double* val,
          int32_t* status, uint8_t* outcome) {
-  extern __shared__ __align__(16) uint8_t smem[];
-  const uint32_t wb = (uint32_t)__cvta_generic_to_shared(smem) + (threadIdx.x >> 5) * kWarpBufAlloc;
+  const uint32_t wb = (uint32_t)__cvta_generic_to_shared(g_smem) + (threadIdx.x >> 5) * kWarpBufAlloc;
   const uint32_t cs = min(n, blockIdx.x * chunk), ce = min(n, cs + chunk);
   if (cs >= ce) return;
   ColumnSink sink{S, kh, val, status, outcome};
@@ -856,14 +856,12 @@ __global__ void __launch_bounds__(kColThreads, 1)
 k_process_columns(const __grid_constant__ DevSchema S, const __grid_constant__ DevTables T,
                   const uint64_t* __restrict__ kh, const uint64_t* __restrict__ ts,
                   const double* __restrict__ val, uint64_t n, uint64_t chunk, uint32_t ns) {
-  extern __shared__ __align__(16) uint8_t smem[];
-  __shared__ uint32_t s_cnt[8];
-  const SmemTable M = smem_table_carve<false>(smem, ns, (S.ops & BH_OP_HIST) != 0);
+  const SmemTable M = smem_table_carve<false>(ns, (S.ops & BH_OP_HIST) != 0);
   smem_table_clear<false>(M);
-  if (threadIdx.x < 8) s_cnt[threadIdx.x] = 0;
+  if (threadIdx.x < 8) g_cnt[threadIdx.x] = 0;
   __syncthreads();
   const uint64_t cs = min(n, (uint64_t)blockIdx.x * chunk), ce = min(n, cs + chunk);
-  LaneCounters C{0u, s_cnt};
+  LaneCounters C{0u};
   uint64_t wbase = 0;
   if (cs < ce && S.has_window) { uint64_t w0 = div64(ts[cs], S.wdiv); wbase = w0 ? w0 - 1 : 0; }
   const bool need_value = (S.ops & (BH_OP_SUM | BH_OP_MIN | BH_OP_MAX | BH_OP_HIST)) != 0;
@@ -886,7 +884,7 @@ k_process_columns(const __grid_constant__ DevSchema S, const __grid_constant__ D
   }
   __syncthreads();
   smem_table_flush<false>(S, T, M, wbase);
-  counters_flush(T, C, s_cnt);
+  counters_flush(T, C);
 }
 
 // =========================================================================================
