@@ -689,17 +689,19 @@ __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefe
 // coalesced copy of payload[A, B) (both multiples of 16) into the skewed warp buffer
 __device__ __forceinline__ void stage_range(const uint8_t* __restrict__ payload, uint32_t A, uint32_t B, uint32_t wb,
                                             uint32_t lane) {
-  const uint4* src = reinterpret_cast<const uint4*>(payload + A);
+  const uint4* src = reinterpret_cast<const uint4*>(payload + A) + lane;
   const uint32_t nvec = (B - A) >> 4;
+  // lane l copies chunks l, l+32, ...: 32 chunks = 512 B = 8 blocks of 64, so the skewed destination
+  // advances by 512 + 8*4 = 544 bytes per step (a 16-byte chunk never straddles a 64-byte block)
+  const uint32_t d0 = wb + skew(lane << 4);
   uint4 v[kWarpChunks];
 #pragma unroll
   for (uint32_t k = 0; k < kWarpChunks; k++)
-    if (lane + 32 * k < nvec) v[k] = ldg_stream(src + lane + 32 * k);
+    if (lane + 32 * k < nvec) v[k] = ldg_stream(src + 32 * k);
 #pragma unroll
   for (uint32_t k = 0; k < kWarpChunks; k++) {
-    const uint32_t i = lane + 32 * k;
-    if (i < nvec) {
-      const uint32_t d = wb + skew(i << 4);   // a 16-byte chunk never straddles a 64-byte block
+    if (lane + 32 * k < nvec) {
+      const uint32_t d = d0 + 544u * k;
       sts32(d, v[k].x); sts32(d + 4, v[k].y); sts32(d + 8, v[k].z); sts32(d + 12, v[k].w);
     }
   }
