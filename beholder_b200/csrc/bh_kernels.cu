@@ -286,11 +286,13 @@ __device__ __forceinline__ void sts32(uint32_t a, uint32_t v) { asm volatile("st
 __device__ __forceinline__ uint32_t skew(uint32_t a) { return a + ((a >> 6) << 2); }
 
 struct SmemRd {           // event bytes staged (skewed) in shared memory
-  uint32_t base;          // shared-window address of the warp buffer
-  uint32_t off;           // logical offset of this event's first byte in the buffer
-  __device__ __forceinline__ uint32_t b(uint32_t i) const { return lds8(base + skew(off + i)); }
-  __device__ __forceinline__ uint32_t ab(uint32_t lp) const { return lds8(base + skew(lp)); }   // absolute logical position
-  __device__ __forceinline__ uint32_t w32(uint32_t a) const { return lds32(base + skew(a)); }   // aligned logical word
+  // Positions are in the warp buffer's "origin space": the buffer's shared-window address is a multiple
+  // of 68, so a logical origin Q (a multiple of 64) exists with skew(Q + x) = address of logical byte x,
+  // and a byte access is skew() plus the load, with no base register to add.
+  uint32_t off;           // origin-space position of this event's first byte
+  __device__ __forceinline__ uint32_t b(uint32_t i) const { return lds8(skew(off + i)); }
+  __device__ __forceinline__ uint32_t ab(uint32_t lp) const { return lds8(skew(lp)); }   // absolute position
+  __device__ __forceinline__ uint32_t w32(uint32_t a) const { return lds32(skew(a)); }   // aligned word
   __device__ __forceinline__ uint64_t le64(uint32_t i, uint32_t nvalid) const {
     uint32_t a = off + i;
     uint32_t sh = (a & 3u) * 8u;
@@ -673,7 +675,14 @@ __device__ __noinline__ uint32_t decode_and_check_gmem(const DevSchema& S, const
 // =========================================================================================
 constexpr uint32_t kWarpBuf = 2304;                                  // payload bytes staged per warp batch (32 x 72)
 constexpr uint32_t kWarpChunks = (kWarpBuf / 16 + 1 + 31) / 32;      // 16-byte chunks per lane (5)
-constexpr uint32_t kWarpBufAlloc = kWarpBuf + kWarpBuf / 16 + 64;    // + skew padding + over-read slack
+constexpr uint32_t kWarpBufAlloc = ((kWarpBuf + kWarpBuf / 16 + 64 + 67) / 68) * 68;   // + skew padding + over-read slack, multiple of 68
+constexpr uint32_t kWarpBufSlack = 68;   // the first warp buffer is moved up to a multiple of 68
+
+// origin (see SmemRd) of the calling warp's buffer; `first` = shared-window address where warp buffers may start
+__device__ __forceinline__ uint32_t warp_buffer_origin(uint32_t first) {
+  const uint32_t m = (first + 67u) / 68u + (threadIdx.x >> 5) * (kWarpBufAlloc / 68u);
+  return m << 6;
+}
 constexpr int kRawThreads = 1024;      // decode-only kernel and the integer-table fused kernel
 constexpr int kRawThreadsF64 = 768;    // fused kernel with the (larger) f64 table: fewer warp buffers, 4096 slots still fit
 
@@ -686,14 +695,14 @@ __device__ __forceinline__ uint4 ldg_stream(const uint4* p) {
 constexpr uint32_t kPrefetchAhead = 4;   // batches ahead whose cache lines are pulled into L2
 __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" :: "l"(p)); }
 
-// coalesced copy of payload[A, B) (both multiples of 16) into the skewed warp buffer
+// coalesced copy of payload[A, B) (both multiples of 16) into the skewed warp buffer with origin `wb`
 __device__ __forceinline__ void stage_range(const uint8_t* __restrict__ payload, uint32_t A, uint32_t B, uint32_t wb,
                                             uint32_t lane) {
   const uint4* src = reinterpret_cast<const uint4*>(payload + A) + lane;
   const uint32_t nvec = (B - A) >> 4;
   // lane l copies chunks l, l+32, ...: 32 chunks = 512 B = 8 blocks of 64, so the skewed destination
   // advances by 512 + 8*4 = 544 bytes per step (a 16-byte chunk never straddles a 64-byte block)
-  const uint32_t d0 = wb + skew(lane << 4);
+  const uint32_t d0 = skew(wb + (lane << 4));
   uint4 v[kWarpChunks];
 #pragma unroll
   for (uint32_t k = 0; k < kWarpChunks; k++)
@@ -763,7 +772,7 @@ __device__ __forceinline__ void raw_warp_loop(const DevSchema& S, const uint8_t*
         __syncwarp();
         const bool mine = valid && (!BIG || (lane / g) == q);
         const uint32_t mask = __ballot_sync(0xFFFFFFFFu, mine);
-        if (mine) { SmemRd r{wb, o0 - A}; outcome = decode_and_check_smem(S, r, o1 - o0, kh, value, ival, status, mask); }
+        if (mine) { SmemRd r{wb + (o0 - A)}; outcome = decode_and_check_smem(S, r, o1 - o0, kh, value, ival, status, mask); }
         __syncwarp();                               // the buffer is rewritten by the next part / batch
         if (!BIG) break;
       }
@@ -805,8 +814,8 @@ k_process_raw(const __grid_constant__ DevSchema S, const __grid_constant__ DevTa
               const uint64_t* __restrict__ ts, uint32_t n, uint32_t chunk, uint32_t ns) {
   const bool hist = (S.ops & BH_OP_HIST) != 0;
   const SmemTable M = smem_table_carve<INTV>(ns, hist);
-  const uint32_t wb = (uint32_t)__cvta_generic_to_shared(g_smem) + ((ns * smem_slot_bytes(INTV, hist) + 15u) & ~15u) +
-                      (threadIdx.x >> 5) * kWarpBufAlloc;
+  const uint32_t wb = warp_buffer_origin((uint32_t)__cvta_generic_to_shared(g_smem) +
+                                         ((ns * smem_slot_bytes(INTV, hist) + 15u) & ~15u));
   smem_table_clear<INTV>(M);
   if (threadIdx.x < 8) g_cnt[threadIdx.x] = 0;
   __syncthreads();
@@ -842,7 +851,7 @@ __global__ void __launch_bounds__(kRawThreads, 1)
 k_decode(const __grid_constant__ DevSchema S, const uint8_t* __restrict__ payload,
          const uint32_t* __restrict__ offsets, uint32_t n, uint32_t chunk, uint64_t* kh, double* val,
          int32_t* status, uint8_t* outcome) {
-  const uint32_t wb = (uint32_t)__cvta_generic_to_shared(g_smem) + (threadIdx.x >> 5) * kWarpBufAlloc;
+  const uint32_t wb = warp_buffer_origin((uint32_t)__cvta_generic_to_shared(g_smem));
   const uint32_t cs = min(n, blockIdx.x * chunk), ce = min(n, cs + chunk);
   if (cs >= ce) return;
   ColumnSink sink{S, kh, val, status, outcome};
@@ -1028,7 +1037,7 @@ cudaError_t launch_process_raw(const DevSchema& S, const DevTables& T, const Lau
   if (n == 0) return cudaSuccess;
   const bool hist = (S.ops & BH_OP_HIST) != 0, intv = S.int_values != 0;
   const uint32_t threads = intv ? kRawThreads : kRawThreadsF64;
-  size_t wbytes = (size_t)(threads / 32) * kWarpBufAlloc;
+  size_t wbytes = (size_t)(threads / 32) * kWarpBufAlloc + kWarpBufSlack;
   uint32_t ns = pick_smem_slots(intv, hist, G, wbytes);
   size_t smem = (((size_t)ns * smem_slot_bytes(intv, hist) + 15) & ~(size_t)15) + wbytes;
   uint32_t grid = (uint32_t)G.sms;
@@ -1049,7 +1058,7 @@ cudaError_t launch_decode(const DevSchema& S, const LaunchGeom& G, const uint8_t
                           const uint32_t* offsets, uint32_t n, uint64_t* kh, double* val,
                           int32_t* status, uint8_t* outcome, cudaStream_t st) {
   if (n == 0) return cudaSuccess;
-  size_t smem = (size_t)(kRawThreads / 32) * kWarpBufAlloc;
+  size_t smem = (size_t)(kRawThreads / 32) * kWarpBufAlloc + kWarpBufSlack;
   uint32_t grid = (uint32_t)G.sms;
   uint32_t need = (n + kRawThreads - 1) / kRawThreads;
   if (need < grid) grid = need;
