@@ -703,10 +703,14 @@ __device__ __forceinline__ void stage_range(const uint8_t* __restrict__ payload,
   // lane l copies chunks l, l+32, ...: 32 chunks = 512 B = 8 blocks of 64, so the skewed destination
   // advances by 512 + 8*4 = 544 bytes per step (a 16-byte chunk never straddles a 64-byte block)
   const uint32_t d0 = skew(wb + (lane << 4));
+  // zero first: a chunk that is skipped must not leave its registers "carried" around the batch loop
+  // (the compiler then keeps the stale values alive with moves and local-memory spills)
   uint4 v[kWarpChunks];
 #pragma unroll
-  for (uint32_t k = 0; k < kWarpChunks; k++)
+  for (uint32_t k = 0; k < kWarpChunks; k++) {
+    v[k] = make_uint4(0u, 0u, 0u, 0u);
     if (lane + 32 * k < nvec) v[k] = ldg_stream(src + 32 * k);
+  }
 #pragma unroll
   for (uint32_t k = 0; k < kWarpChunks; k++) {
     if (lane + 32 * k < nvec) {
