@@ -76,30 +76,32 @@ __shared__ uint32_t g_cnt[8];
 
 struct SmemTable {
   // Only the slot count is kept; the column arrays are found from it and the shared base at
-  // each use: key u64[ns] | INTV: sum_lo u32, sum_hi i32, min i32, max i32 / F64: sum f64, min_inv u64,
-  // max_ord u64 | cnt u32[ns] | gslot u32[ns] (histograms only) | wrel u8[ns]
+  // each use: tag u32[ns] | key u64[ns] | INTV: sum_lo u32, sum_hi i32, min i32, max i32 / F64: sum f64,
+  // min_inv u64, max_ord u64 | cnt u32[ns] | gslot u32[ns] (histograms only)
+  // tag = window byte << 24 | 24 bits of the key hash that do not take part in the slot index;
+  // 0xFFFFFFFF = empty slot (the window byte is always < 255).
   uint32_t ns;              // power of two
   uint32_t shift;           // 32 - log2(ns)
   uint32_t hist;            // gslot column present
-  __device__ __forceinline__ unsigned long long* key() const { return (unsigned long long*)g_smem; }
-  template <bool INTV> __device__ __forceinline__ uint8_t* vals() const { return g_smem + (size_t)ns * 8; }
-  template <bool INTV> __device__ __forceinline__ uint32_t* cnt() const { return (uint32_t*)(g_smem + (size_t)ns * (INTV ? 24 : 32)); }
-  template <bool INTV> __device__ __forceinline__ uint32_t* gslot() const { return hist ? (uint32_t*)(g_smem + (size_t)ns * (INTV ? 28 : 36)) : nullptr; }
-  template <bool INTV> __device__ __forceinline__ uint8_t* wrel() const { return g_smem + (size_t)ns * ((INTV ? 28 : 36) + (hist ? 4 : 0)); }
+  __device__ __forceinline__ uint32_t* tag() const { return (uint32_t*)g_smem; }
+  __device__ __forceinline__ unsigned long long* key() const { return (unsigned long long*)(g_smem + (size_t)ns * 4); }
+  template <bool INTV> __device__ __forceinline__ uint32_t* cnt() const { return (uint32_t*)(g_smem + (size_t)ns * (INTV ? 28 : 36)); }
+  template <bool INTV> __device__ __forceinline__ uint32_t* gslot() const { return hist ? (uint32_t*)(g_smem + (size_t)ns * (INTV ? 32 : 40)) : nullptr; }
   // INTV value columns
-  __device__ __forceinline__ uint32_t* sum_lo() const { return (uint32_t*)(g_smem + (size_t)ns * 8); }
-  __device__ __forceinline__ int32_t* sum_hi() const { return (int32_t*)(g_smem + (size_t)ns * 12); }
-  __device__ __forceinline__ int32_t* imin() const { return (int32_t*)(g_smem + (size_t)ns * 16); }
-  __device__ __forceinline__ int32_t* imax() const { return (int32_t*)(g_smem + (size_t)ns * 20); }
+  __device__ __forceinline__ uint32_t* sum_lo() const { return (uint32_t*)(g_smem + (size_t)ns * 12); }
+  __device__ __forceinline__ int32_t* sum_hi() const { return (int32_t*)(g_smem + (size_t)ns * 16); }
+  __device__ __forceinline__ int32_t* imin() const { return (int32_t*)(g_smem + (size_t)ns * 20); }
+  __device__ __forceinline__ int32_t* imax() const { return (int32_t*)(g_smem + (size_t)ns * 24); }
   // F64 value columns
-  __device__ __forceinline__ double* fsum() const { return (double*)(g_smem + (size_t)ns * 8); }
-  __device__ __forceinline__ unsigned long long* fmin_inv() const { return (unsigned long long*)(g_smem + (size_t)ns * 16); }
-  __device__ __forceinline__ unsigned long long* fmax_ord() const { return (unsigned long long*)(g_smem + (size_t)ns * 24); }
+  __device__ __forceinline__ double* fsum() const { return (double*)(g_smem + (size_t)ns * 12); }
+  __device__ __forceinline__ unsigned long long* fmin_inv() const { return (unsigned long long*)(g_smem + (size_t)ns * 20); }
+  __device__ __forceinline__ unsigned long long* fmax_ord() const { return (unsigned long long*)(g_smem + (size_t)ns * 28); }
 };
 constexpr int kSmemProbes = 16;
-constexpr uint32_t kWrelUnset = 0xFFu;   // window byte of a claimed slot that its owner has not filled in yet
+constexpr uint32_t kTagEmpty = 0xFFFFFFFFu;
+__device__ __forceinline__ uint32_t smem_tag(uint64_t kh, uint32_t wrel) { return (wrel << 24) | (uint32_t)(kh >> 40); }
 __host__ __device__ constexpr uint32_t smem_slot_bytes(bool intv, bool hist) {
-  return 8 + (intv ? 16 : 24) + 4 + 1 + (hist ? 4 : 0);
+  return 4 + 8 + (intv ? 16 : 24) + 4 + (hist ? 4 : 0);
 }
 
 template <bool INTV>
@@ -113,7 +115,7 @@ __device__ __forceinline__ SmemTable smem_table_carve(uint32_t ns, bool hist) {
 template <bool INTV>
 __device__ __forceinline__ void smem_table_clear(const SmemTable& M) {
   for (uint32_t i = threadIdx.x; i < M.ns; i += blockDim.x) {
-    M.key()[i] = kEmptyKey; M.cnt<INTV>()[i] = 0; M.wrel<INTV>()[i] = (uint8_t)kWrelUnset;
+    M.tag()[i] = kTagEmpty; M.key()[i] = kEmptyKey; M.cnt<INTV>()[i] = 0;
     if (M.hist) M.gslot<INTV>()[i] = 0;
     if (INTV) { M.sum_lo()[i] = 0; M.sum_hi()[i] = 0; M.imin()[i] = 0x7FFFFFFF; M.imax()[i] = (int32_t)0x80000000; }
     else { M.fsum()[i] = 0.0; M.fmin_inv()[i] = 0; M.fmax_ord()[i] = 0; }
@@ -121,33 +123,36 @@ __device__ __forceinline__ void smem_table_clear(const SmemTable& M) {
 }
 
 // returns the shared slot, or -1 when the event has to go to the HBM table directly.
-// Claiming a slot is ONE compare-and-swap on the key word (empty -> key); the window byte follows with a
-// plain store and readers that match the key wait for it (0xFF = not written yet).  No fence is needed:
-// only the one location is polled.  With histograms on, the HBM slot must be visible before the window
-// byte, which costs a block-level fence on that (rare) path only.
+// The look-up walks the 32-bit TAG column only: one load and two compares per probe; the 64-bit key is read
+// once, when a tag matches.  Claiming a slot is ONE compare-and-swap on the tag (empty -> tag); the key
+// follows with a plain store and readers that match the tag wait for it (all-ones = not written yet).  No
+// fence is needed: only the one location is polled.  A reader that saw a torn or foreign key just walks on
+// and may claim a second slot for the same (key, window): harmless, the flush merges both into the HBM
+// entry.  With histograms on, the HBM slot must be visible before the key, which costs a block-level fence
+// on that (rare) path only.
 // Slow half: claim a slot (or find the key someone else is inserting right now), starting at `slot`.
 // Kept out of line: the CAS and the wait loop make the compiler add yields and convergence barriers
 // that must not sit in the hot look-up loop.
 template <bool INTV>
-__device__ __noinline__ int smem_insert(const SmemTable M, const DevTables& T, uint64_t kh, uint32_t wrel,
+__device__ __noinline__ int smem_insert(const SmemTable M, const DevTables& T, uint64_t kh, uint32_t tag,
                                         uint64_t win, uint32_t slot, int probes_left) {
   volatile unsigned long long* vkey = M.key();
-  volatile uint8_t* vwrel = M.wrel<INTV>();
+  volatile uint32_t* vtag = M.tag();
 #pragma unroll 1
   for (int p = 0; p < probes_left; p++) {
-    unsigned long long k = vkey[slot];
-    if (k == kEmptyKey) {
-      k = atomicCAS(&M.key()[slot], (unsigned long long)kEmptyKey, (unsigned long long)kh);
-      if (k == kEmptyKey) {     // claimed
+    uint32_t t = vtag[slot];
+    if (t == kTagEmpty) {
+      t = atomicCAS(&M.tag()[slot], kTagEmpty, tag);
+      if (t == kTagEmpty) {     // claimed
         if (M.hist) { uint32_t r; M.gslot<INTV>()[slot] = g_find_or_insert(T, win, kh, &r); __threadfence_block(); }
-        vwrel[slot] = (uint8_t)wrel;
+        vkey[slot] = kh;
         return (int)slot;
       }
     }
-    if (k == kh) {
-      uint32_t w = vwrel[slot];
-      while (w == kWrelUnset) w = vwrel[slot];
-      if (w == wrel) return (int)slot;
+    if (t == tag) {
+      unsigned long long k = vkey[slot];
+      while (k == kEmptyKey) k = vkey[slot];
+      if (k == kh) return (int)slot;
     }
     slot = (slot + 1) & (M.ns - 1);
   }
@@ -158,19 +163,21 @@ __device__ __noinline__ int smem_insert(const SmemTable M, const DevTables& T, u
 template <bool INTV>
 __device__ __forceinline__ int smem_find_or_insert(const SmemTable& M, const DevTables& T, uint64_t kh,
                                                    uint32_t wrel, uint64_t win) {
-  uint32_t x = (uint32_t)kh ^ (uint32_t)(kh >> 32) ^ (wrel * 0x85EBCA6Bu);
+  const uint32_t x = (uint32_t)kh ^ (uint32_t)(kh >> 32) ^ (wrel * 0x85EBCA6Bu);
   uint32_t slot = (x * 0x9E3779B1u) >> M.shift;
-  int p = 0;
+  const uint32_t tag = smem_tag(kh, wrel), mask = M.ns - 1;
+  const uint32_t* tags = M.tag();
+  uint32_t t = tags[slot];
+  int left = kSmemProbes;
 #pragma unroll 1
-  for (; p < kSmemProbes; p++) {
-    const unsigned long long k = M.key()[slot];
-    const uint32_t w = M.wrel<INTV>()[slot];
-    if (k == kh && w == wrel) return (int)slot;
-    if (k == kEmptyKey || (k == kh && w == kWrelUnset)) break;   // not here (yet): go and insert / wait
-    slot = (slot + 1) & (M.ns - 1);
+  while (t != tag && t != kTagEmpty) {
+    if (--left == 0) return -1;
+    slot = (slot + 1) & mask;
+    t = tags[slot];
   }
-  if (p == kSmemProbes) return -1;
-  return smem_insert<INTV>(M, T, kh, wrel, win, slot, kSmemProbes - p);
+  if (t == tag && M.key()[slot] == kh) return (int)slot;
+  // empty slot, key not stored yet, or another key with the same tag: the out-of-line half sorts it out
+  return smem_insert<INTV>(M, T, kh, tag, win, slot, left);
 }
 
 // Outcome counters of a CTA.  Only the count of aggregated events lives in a register; drops, spills
@@ -243,7 +250,7 @@ __device__ __forceinline__ void smem_table_flush(const DevSchema& S, const DevTa
     unsigned long long k = M.key()[i];
     uint32_t c = M.cnt<INTV>()[i];
     if (k == kEmptyKey || c == 0) continue;
-    uint64_t win = wbase + M.wrel<INTV>()[i];
+    uint64_t win = wbase + (M.tag()[i] >> 24);
     uint32_t r = (uint32_t)win & (T.ring - 1);
     uint32_t gs = M.hist ? M.gslot<INTV>()[i] : g_find_or_insert(T, win, k, &r);
     if (gs >= kGslotWindow) {
@@ -643,7 +650,7 @@ __device__ __forceinline__ uint32_t finish_event(const DevSchema& S, const Parse
 }
 
 constexpr uint32_t kSlowDecode = 0x100u;   // outcome flag: the message left the straight path (diagnostic counter)
-__device__ __noinline__ bool decode_slow(const DevSchema& S, const SmemRd& r, uint32_t len, Parsed& P) {
+__device__ __noinline__ bool decode_slow(const DevSchema& S, const SmemRd r, uint32_t len, Parsed& P) {
   return decode_fast(S, r, len, P) || decode_event(S, r, len, P);
 }
 
@@ -661,13 +668,16 @@ __device__ __forceinline__ uint32_t decode_and_check_smem(const DevSchema& S, co
   return finish_event(S, P, value, ival, status) | slow;
 }
 
-__device__ __noinline__ uint32_t decode_and_check_gmem(const DevSchema& S, const uint8_t* p, uint32_t len, uint64_t& kh,
-                                                       double& value, int32_t& ival, uint32_t& status) {
+// Out of line (rare): results come back through one small object, so that the caller's own
+// kh/value/ival/status never have their address taken and stay in registers.
+struct EventOut { uint64_t kh; double value; int32_t ival; uint32_t status; };
+__device__ __noinline__ uint32_t decode_and_check_gmem(const DevSchema& S, const uint8_t* p, uint32_t len, EventOut& out) {
   Parsed P;
   GmemRd r{p};
-  if (!decode_event(S, r, len, P)) { kh = 0; value = 0.0; ival = 0; status = 0; return BH_EV_DROP_DECODE; }
-  kh = event_key_hash(S, r, P);
-  return finish_event(S, P, value, ival, status);
+  out.kh = 0; out.value = 0.0; out.ival = 0; out.status = 0;
+  if (!decode_event(S, r, len, P)) return BH_EV_DROP_DECODE;
+  out.kh = event_key_hash(S, r, P);
+  return finish_event(S, P, out.value, out.ival, out.status);
 }
 
 // =========================================================================================
@@ -781,7 +791,9 @@ __device__ __forceinline__ void raw_warp_loop(const DevSchema& S, const uint8_t*
         if (!BIG) break;
       }
     } else if (valid && sane) {
-      outcome = decode_and_check_gmem(S, payload + o0, o1 - o0, kh, value, ival, status);
+      EventOut out;
+      outcome = decode_and_check_gmem(S, payload + o0, o1 - o0, out);
+      kh = out.kh; value = out.value; ival = out.ival; status = out.status;
     }
     sink.event(valid, e, outcome, kh, value, ival, status, aux);
   }
