@@ -708,19 +708,18 @@ __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefe
 // coalesced copy of payload[A, B) (both multiples of 16) into the skewed warp buffer with origin `wb`
 __device__ __forceinline__ void stage_range(const uint8_t* __restrict__ payload, uint32_t A, uint32_t B, uint32_t wb,
                                             uint32_t lane) {
-  const uint4* src = reinterpret_cast<const uint4*>(payload + A) + lane;
+  const uint4* src = reinterpret_cast<const uint4*>(payload + A);
   const uint32_t nvec = (B - A) >> 4;
+  if (nvec == 0) return;
   // lane l copies chunks l, l+32, ...: 32 chunks = 512 B = 8 blocks of 64, so the skewed destination
   // advances by 512 + 8*4 = 544 bytes per step (a 16-byte chunk never straddles a 64-byte block)
   const uint32_t d0 = skew(wb + (lane << 4));
-  // zero first: a chunk that is skipped must not leave its registers "carried" around the batch loop
-  // (the compiler then keeps the stale values alive with moves and local-memory spills)
+  // Every load is issued, past-the-end chunks re-reading the last one (same cache line as a neighbour's,
+  // so no extra traffic): a load under `if` leaves registers that are undefined on one path, and the
+  // compiler then carries them around the batch loop with moves and spills (20 registers' worth).
   uint4 v[kWarpChunks];
 #pragma unroll
-  for (uint32_t k = 0; k < kWarpChunks; k++) {
-    v[k] = make_uint4(0u, 0u, 0u, 0u);
-    if (lane + 32 * k < nvec) v[k] = ldg_stream(src + 32 * k);
-  }
+  for (uint32_t k = 0; k < kWarpChunks; k++) v[k] = ldg_stream(src + min(lane + 32 * k, nvec - 1));
 #pragma unroll
   for (uint32_t k = 0; k < kWarpChunks; k++) {
     if (lane + 32 * k < nvec) {
