@@ -269,6 +269,7 @@ int bh_create(const bh_config* cfg, bh_ctx** out) {
 #define CUB_(call) do { cudaError_t e__ = (call); if (e__ != cudaSuccess) { fail(c, BH_ERR_CUDA, "%s: %s", #call, cudaGetErrorString(e__)); return bail(e__ == cudaErrorMemoryAllocation ? BH_ERR_NOMEM : BH_ERR_CUDA); } } while (0)
   c->G.sms = prop.multiProcessorCount;
   c->G.smem_optin = (int)prop.sharedMemPerBlockOptin;
+  { const char* g = getenv("BEHOLDER_GENERIC_KERNELS"); c->G.generic_only = (g && g[0] == '1') || (cfg->flags & BH_F_GENERIC_KERNELS); }
   CUB_(cudaStreamCreateWithFlags(&c->st_compute, cudaStreamNonBlocking));
   CUB_(cudaStreamCreateWithFlags(&c->st_copy[0], cudaStreamNonBlocking));
   CUB_(cudaStreamCreateWithFlags(&c->st_copy[1], cudaStreamNonBlocking));

@@ -114,6 +114,10 @@ struct DevSchema {
   uint32_t tag_key0, tag_status, tag_value;   // their canonical one-byte tags (0xFFFFFFFF = none)
   uint32_t big_messages;     // messages above ~72 B expected: kernels that stage a batch in parts
   Div64 wdiv;
+  // array members through functions: the compile-time schema view (ProgressSchema) offers the same names
+  __host__ __device__ __forceinline__ uint32_t field(uint32_t number) const { return fld[number]; }
+  __host__ __device__ __forceinline__ uint32_t part_len(int k) const { return part_is_len[k]; }
+  __host__ __device__ __forceinline__ uint32_t part_fld(int k) const { return part_field[k]; }
 };
 
 struct Stat {            // 32 B = one L2 sector; zero-initialised

@@ -541,7 +541,47 @@ __device__ __forceinline__ bool decode_fast(const DevSchema& S, const SmemRd& r,
 // brings them back together — without it the compiler reconverges only at the end and the rest of the
 // decoder plus the key hash run once per divergent group (measured: 40 % slower on mixed streams).
 // Hence no early return before the last section: failures are carried in `ok`.
-__device__ __forceinline__ bool decode_straight(const DevSchema& S, const SmemRd& r, uint32_t len, Parsed& P, uint32_t mask) {
+// Compile-time view of the reference's own message and grouping: api.TelemetryProgress { mediaId = 1 string,
+// status = 2 enum, progress = 3 int32, host = 4 string } (index.js:46,131; numbers ASSUMED, see schema.py),
+// grouped by (mediaId, status) in tumbling windows with the enum drop on.  Everything the decoder asks the
+// schema is a constant here, so the straight-line decoder, the key hash and the drop rules lose their table
+// look-ups and tests; what varies at run time (ops, enum mask, hash seed, window divisor) still comes from the
+// DevSchema.  The host launches the kernel built on this view only when progress_schema_matches() says that
+// the run-time schema is exactly this one; every other schema runs the same code on the DevSchema itself.
+struct ProgressSchema {
+  const DevSchema& dyn;
+  __device__ __forceinline__ operator const DevSchema&() const { return dyn; }
+  static constexpr uint32_t kFld1 = BH_K_STRING | (BH_R_KEY << 8) | (1u << 16);
+  static constexpr uint32_t kFld2 = BH_K_INT32 | ((BH_R_KEY | BH_R_STATUS) << 8) | (2u << 16);
+  static constexpr uint32_t kFld3 = BH_K_INT32 | (BH_R_VALUE << 8);
+  static constexpr uint32_t kFld4 = BH_K_STRING;
+  __host__ __device__ static constexpr uint32_t field(uint32_t n) {
+    return n == 1 ? kFld1 : n == 2 ? kFld2 : n == 3 ? kFld3 : n == 4 ? kFld4 : 0u;
+  }
+  __host__ __device__ static constexpr uint32_t part_len(int k) { return k == 0 ? 1u : 0u; }
+  __host__ __device__ static constexpr uint32_t part_fld(int k) { return k == 0 ? 1u : k == 1 ? 2u : 0u; }
+  static constexpr uint32_t n_parts = 2, identity_key = 0, status_part = 0, has_enum = 1, has_window = 1;
+  static constexpr uint32_t int_values = 1, fast_key0 = 1, fast_status = 2, fast_status_part = 2, fast_value = 3;
+  static constexpr uint32_t fast_value_f64 = 0, tag_key0 = 0x0A, tag_status = 0x10, tag_value = 0x18;
+  // run-time items
+  uint32_t ops; uint64_t enum_mask, hash_seed; Div64 wdiv;
+  __device__ __forceinline__ explicit ProgressSchema(const DevSchema& S)
+      : dyn(S), ops(S.ops), enum_mask(S.enum_mask), hash_seed(S.hash_seed), wdiv(S.wdiv) {}
+};
+
+bool progress_schema_matches(const DevSchema& S) {
+  typedef ProgressSchema P;
+  for (uint32_t n = 0; n < 32; n++) if (S.fld[n] != P::field(n)) return false;
+  for (int k = 0; k < (int)P::n_parts; k++) if (S.part_is_len[k] != P::part_len(k) || S.part_field[k] != P::part_fld(k)) return false;
+  return S.n_parts == P::n_parts && S.identity_key == P::identity_key && S.status_part == P::status_part &&
+         S.has_enum == P::has_enum && S.has_window == P::has_window && S.int_values == P::int_values &&
+         S.fast_key0 == P::fast_key0 && S.fast_status == P::fast_status && S.fast_status_part == P::fast_status_part &&
+         S.fast_value == P::fast_value && S.fast_value_f64 == P::fast_value_f64 && S.tag_key0 == P::tag_key0 &&
+         S.tag_status == P::tag_status && S.tag_value == P::tag_value && S.mode == BH_MODE_WINDOWED;
+}
+
+template <class SC>
+__device__ __forceinline__ bool decode_straight(const SC& S, const SmemRd& r, uint32_t len, Parsed& P, uint32_t mask) {
   uint32_t lp = r.off;
   const uint32_t end = lp + len;
   uint32_t t = r.ab(lp), n = r.ab(lp + 1);
@@ -551,7 +591,7 @@ __device__ __forceinline__ bool decode_straight(const DevSchema& S, const SmemRd
   // role-less strings (clamped) and unknown length-delimited fields (strict): skipped wherever they stand
   auto skip_plain = [&]() {
     while (ok && lp < end) {
-      const uint32_t f = (t & 0x80u) ? 0xFFFFu : S.fld[t >> 3];
+      const uint32_t f = (t & 0x80u) ? 0xFFFFu : S.field(t >> 3);
       const bool str = f == (uint32_t)BH_K_STRING, unk = f == 0u && (t & 7u) == 2u;
       if (!(str || unk)) break;                            // a field with a role (or anything unusual): caller decides
       if (lp + 2 > end) { ok = false; break; }
@@ -627,22 +667,24 @@ __device__ __forceinline__ uint64_t hash_span_smem(const SmemRd& r, uint32_t lp,
   return absorb(h, len_word(n, field));
 }
 
-__device__ __forceinline__ uint64_t event_key_hash_smem(const DevSchema& S, const SmemRd& r, const Parsed& P) {
+template <class SC>
+__device__ __forceinline__ uint64_t event_key_hash_smem(const SC& S, const SmemRd& r, const Parsed& P) {
   if (S.status_part) return (uint64_t)P.status;
   if (S.identity_key) return (uint64_t)P.pval[0];
   uint64_t h = S.hash_seed ^ kHashInit;
 #pragma unroll
   for (int k = 0; k < BH_MAX_KEY_PARTS; k++) {
     if ((uint32_t)k >= S.n_parts) break;
-    if (S.part_is_len[k]) h = hash_span_smem(r, r.off + P.ppos[k], P.plen[k], S.part_field[k], h);
-    else h = absorb(h, varint_word(P.pval[k], S.part_field[k]));
+    if (S.part_len(k)) h = hash_span_smem(r, r.off + P.ppos[k], P.plen[k], S.part_fld(k), h);
+    else h = absorb(h, varint_word(P.pval[k], S.part_fld(k)));
   }
   return fmix64(h);
 }
 
 // drop rules after a successful decode.  Returns BH_EV_*.  `ival` is the value for integer value
 // kinds, `value` for the others.
-__device__ __forceinline__ uint32_t finish_event(const DevSchema& S, const Parsed& P, double& value, int32_t& ival, uint32_t& status) {
+template <class SC>
+__device__ __forceinline__ uint32_t finish_event(const SC& S, const Parsed& P, double& value, int32_t& ival, uint32_t& status) {
   value = P.value; ival = (int32_t)P.uval; status = P.status;
   if (S.has_enum && !(P.status < 64 && ((S.enum_mask >> P.status) & 1ull))) return BH_EV_DROP_ENUM;
   if (!S.int_values && (S.ops & (BH_OP_SUM | BH_OP_MIN | BH_OP_MAX | BH_OP_HIST)) && P.value != P.value) return BH_EV_DROP_NAN;
@@ -654,7 +696,8 @@ __device__ __noinline__ bool decode_slow(const DevSchema& S, const SmemRd r, uin
   return decode_fast(S, r, len, P) || decode_event(S, r, len, P);
 }
 
-__device__ __forceinline__ uint32_t decode_and_check_smem(const DevSchema& S, const SmemRd& r, uint32_t len, uint64_t& kh,
+template <class SC>
+__device__ __forceinline__ uint32_t decode_and_check_smem(const SC& S, const SmemRd& r, uint32_t len, uint64_t& kh,
                                                           double& value, int32_t& ival, uint32_t& status, uint32_t mask) {
   Parsed P;
   uint32_t slow = 0;
@@ -734,8 +777,8 @@ __device__ __forceinline__ void stage_range(const uint8_t* __restrict__ payload,
 // coalesced 128-bit loads, then every lane parses its own message.  The offsets of the NEXT batch are
 // loaded before the current one is parsed, and the lines the batch after that will touch are
 // prefetched into L2, so a warp rarely waits for HBM.
-template <bool BIG, class Sink>
-__device__ __forceinline__ void raw_warp_loop(const DevSchema& S, const uint8_t* __restrict__ payload,
+template <bool BIG, class SC, class Sink>
+__device__ __forceinline__ void raw_warp_loop(const SC& S, const uint8_t* __restrict__ payload,
                                               const uint32_t* __restrict__ offsets, uint32_t cs, uint32_t ce,
                                               uint32_t wb, Sink& sink) {
   const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
@@ -798,9 +841,9 @@ __device__ __forceinline__ void raw_warp_loop(const DevSchema& S, const uint8_t*
   }
 }
 
-template <bool INTV>
+template <bool INTV, class SC>
 struct AggSink {
-  const DevSchema& S; const DevTables& T; const SmemTable& M;
+  const SC& S; const DevTables& T; const SmemTable& M;
   const uint64_t* ts; uint64_t wbase; LaneCounters& C;
   __device__ __forceinline__ void prefetch(uint32_t e2, uint32_t lane) const {
     if (S.has_window && ts && lane < 2) prefetch_l2(ts + e2 + lane * 16);
@@ -822,7 +865,18 @@ struct AggSink {
   }
 };
 
-template <bool INTV, bool BIG>
+template <bool INTV, bool BIG, class SC>
+__device__ __forceinline__ void process_chunk(const SC& S, const DevTables& T, const SmemTable& M,
+                                              const uint8_t* __restrict__ payload, const uint32_t* __restrict__ offsets,
+                                              const uint64_t* __restrict__ ts, uint32_t cs, uint32_t ce, uint32_t wb,
+                                              LaneCounters& C, uint64_t& wbase) {
+  if (S.has_window) { uint64_t w0 = div64(ts ? ts[cs] : 0ull, S.wdiv); wbase = w0 ? w0 - 1 : 0; }
+  AggSink<INTV, SC> sink{S, T, M, ts, wbase, C};
+  raw_warp_loop<BIG>(S, payload, offsets, cs, ce, wb, sink);
+}
+
+// PROG: the schema is the reference's own (ProgressSchema) and is read as compile-time constants
+template <bool INTV, bool BIG, bool PROG>
 __global__ void __launch_bounds__(INTV ? kRawThreads : kRawThreadsF64, 1)
 k_process_raw(const __grid_constant__ DevSchema S, const __grid_constant__ DevTables T,
               const uint8_t* __restrict__ payload, const uint32_t* __restrict__ offsets,
@@ -838,9 +892,12 @@ k_process_raw(const __grid_constant__ DevSchema S, const __grid_constant__ DevTa
   LaneCounters C{0u};
   uint64_t wbase = 0;
   if (cs < ce) {
-    if (S.has_window) { uint64_t w0 = div64(ts ? ts[cs] : 0ull, S.wdiv); wbase = w0 ? w0 - 1 : 0; }
-    AggSink<INTV> sink{S, T, M, ts, wbase, C};
-    raw_warp_loop<BIG>(S, payload, offsets, cs, ce, wb, sink);
+    if constexpr (PROG) {
+      const ProgressSchema PS(S);
+      process_chunk<INTV, BIG>(PS, T, M, payload, offsets, ts, cs, ce, wb, C, wbase);
+    } else {
+      process_chunk<INTV, BIG>(S, T, M, payload, offsets, ts, cs, ce, wb, C, wbase);
+    }
   }
   __syncthreads();
   smem_table_flush<INTV>(S, T, M, wbase);
@@ -1029,8 +1086,9 @@ __global__ void k_close_release(const __grid_constant__ DevTables T, uint64_t wi
 // once per device, with that device current (bh_create)
 cudaError_t configure_kernels(const LaunchGeom& G) {
   int dyn = G.smem_optin - 1024;   // leave room for the kernels' static shared memory
-  const void* fns[] = {(const void*)k_process_raw<true, false>, (const void*)k_process_raw<true, true>,
-                       (const void*)k_process_raw<false, false>, (const void*)k_process_raw<false, true>,
+  const void* fns[] = {(const void*)k_process_raw<true, false, false>, (const void*)k_process_raw<true, true, false>,
+                       (const void*)k_process_raw<false, false, false>, (const void*)k_process_raw<false, true, false>,
+                       (const void*)k_process_raw<true, false, true>,
                        (const void*)k_decode<false>, (const void*)k_decode<true>, (const void*)k_process_columns};
   for (const void* f : fns) {
     cudaError_t e = cudaFuncSetAttribute(f, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn);
@@ -1061,10 +1119,13 @@ cudaError_t launch_process_raw(const DevSchema& S, const DevTables& T, const Lau
   uint32_t chunk = (n + grid - 1) / grid;
   chunk = (chunk + 31u) & ~31u;
   const bool big = big_override < 0 ? S.big_messages != 0 : big_override != 0;
-  if (intv && !big) k_process_raw<true, false><<<grid, kRawThreads, smem, st>>>(S, T, payload, offsets, ts, n, chunk, ns);
-  else if (intv) k_process_raw<true, true><<<grid, kRawThreads, smem, st>>>(S, T, payload, offsets, ts, n, chunk, ns);
-  else if (!big) k_process_raw<false, false><<<grid, kRawThreadsF64, smem, st>>>(S, T, payload, offsets, ts, n, chunk, ns);
-  else k_process_raw<false, true><<<grid, kRawThreadsF64, smem, st>>>(S, T, payload, offsets, ts, n, chunk, ns);
+  // the reference's own schema (small messages, integer values): the kernel with the schema folded in
+  const bool prog = intv && !big && !G.generic_only && progress_schema_matches(S);
+  if (prog) k_process_raw<true, false, true><<<grid, kRawThreads, smem, st>>>(S, T, payload, offsets, ts, n, chunk, ns);
+  else if (intv && !big) k_process_raw<true, false, false><<<grid, kRawThreads, smem, st>>>(S, T, payload, offsets, ts, n, chunk, ns);
+  else if (intv) k_process_raw<true, true, false><<<grid, kRawThreads, smem, st>>>(S, T, payload, offsets, ts, n, chunk, ns);
+  else if (!big) k_process_raw<false, false, false><<<grid, kRawThreadsF64, smem, st>>>(S, T, payload, offsets, ts, n, chunk, ns);
+  else k_process_raw<false, true, false><<<grid, kRawThreadsF64, smem, st>>>(S, T, payload, offsets, ts, n, chunk, ns);
   if (launches) (*launches)++;
   return cudaGetLastError();
 }

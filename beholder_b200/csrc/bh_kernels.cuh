@@ -7,7 +7,11 @@ namespace bh {
 struct LaunchGeom {
   int sms;            // SM count of the device
   int smem_optin;     // max opt-in dynamic shared memory per block
+  int generic_only;   // 1 = never launch the kernel specialised on the reference's schema (env BEHOLDER_GENERIC_KERNELS=1; for tests)
 };
+
+// true when S is exactly the schema the specialised fused kernel has compiled in (ProgressSchema)
+bool progress_schema_matches(const DevSchema& S);
 
 // fused proto.decode + enum check + aggregate over one raw batch (index.js:129-138)
 cudaError_t launch_process_raw(const DevSchema& S, const DevTables& T, const LaunchGeom& G,

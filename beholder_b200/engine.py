@@ -42,7 +42,7 @@ class Aggregator:
                  window_ms: int = 10_000, window_ring: int = 0, table_capacity: int = 0,
                  hist_buckets: int = 64, hist_e0: int = DEFAULT_HIST_E0, hash_seed: int = 0xBE401DE5,
                  device: int = 0, slab_bytes: int = 0, slab_events: int = 0, n_slabs: int = 0,
-                 enum_drop: bool = True, message_bytes_hint: int = 0):
+                 enum_drop: bool = True, message_bytes_hint: int = 0, generic_kernels: bool = False):
         schema = schema or telemetry_progress()
         if mode == L.MODE_WINDOWED:
             schema = schema.with_roles(key=key)
@@ -62,6 +62,7 @@ class Aggregator:
         cfg.slab_events = slab_events
         cfg.n_slabs = n_slabs
         cfg.message_bytes_hint = message_bytes_hint
+        cfg.flags = L.F_GENERIC_KERNELS if generic_kernels else 0
         fill_config(cfg, schema)
         if not enum_drop:
             cfg.n_enum = 0

@@ -82,8 +82,15 @@ typedef struct bh_config {
   uint32_t n_slabs;            /* ingest ring depth (0 -> 3) */
   uint32_t message_bytes_hint; /* typical serialized message size; above 72 selects the kernels that stage
                                 * larger messages (results do not depend on it); 0 = small messages */
-  uint32_t reserved0;
+  uint32_t flags;              /* BH_F_* bits */
 } bh_config;
+
+/* bh_config.flags */
+enum {
+  BH_F_GENERIC_KERNELS = 1     /* never launch the fused kernel that has the reference's own schema compiled in
+                                * (api.TelemetryProgress keyed by mediaId + status, int32 progress): same results,
+                                * slower; for tests.  The environment variable BEHOLDER_GENERIC_KERNELS=1 does the same. */
+};
 
 /* One aggregate row.  REFERENCE mode: key_hash = status number, window_id = 0, count = the value of
  * beholder_progress_updates_total{status=<name>} (index.js:30-34). */

@@ -48,6 +48,42 @@ def test_c2_shape_count_sum_min_max(zipf, f64):
     assert len(np.unique(got["window_id"])) >= 10
 
 
+@pytest.mark.parametrize("generic", [False, True])
+@pytest.mark.parametrize("zipf", [False, True])
+def test_schema_specialised_and_generic_kernels_agree(generic, zipf):
+    # int32 progress keyed by (mediaId, status) is the schema one fused kernel has compiled in; the
+    # BH_F_GENERIC_KERNELS flag keeps it out.  Both must match the oracle on a stream with malformed
+    # messages, unknown enum numbers, padded (host) and unpadded messages.
+    for payload in (0, 64):
+        spec = SynthSpec(n_keys=700, rate_per_ms=10, zipf=zipf, payload_bytes=payload,
+                         malformed_ppm=20_000, unknown_enum_ppm=20_000)
+        got, a, k = _run_raw(spec, 300_000, ALL_OPS, generic_kernels=generic)
+        assert_records_equal(got, a.snapshot(), ALL_OPS)
+        d = a.dropped()
+        assert (k["dropped_decode"], k["dropped_enum"], k["dropped_nan"]) == (d["decode"], d["enum"], d["nan"])
+        assert k["events_ok"] == int(a.snapshot()["count"].sum())
+
+
+@pytest.mark.parametrize("generic", [False, True])
+def test_kat_messages_windowed_both_kernels(generic):
+    # the decoder known-answer messages (odd wire types, groups, unknown fields, truncations) as one
+    # batch, repeated so that several warps see them, through the windowed path
+    payloads = [bytes.fromhex(c["payload"]) for c in load_json("kat_decode.json")["default"]] * 40
+    slab, off = pack(payloads)
+    ts = (np.arange(len(payloads), dtype=np.uint64) * 3) + 1_700_000_000_000
+    schema = bh.telemetry_progress()
+    with bh.Aggregator(schema, mode=L.MODE_WINDOWED, key=KEY, ops=ALL_OPS, window_ms=1000, table_capacity=256,
+                       generic_kernels=generic) as g:
+        g.push_batch(slab, off, ts)
+        g.flush()
+        got = g.snapshot_all()
+        k = g.counters(check=False)
+    a = _oracle(schema, ALL_OPS, 1000, slab, off, ts, threads=1)
+    assert_records_equal(got, a.snapshot(), ALL_OPS)
+    d = a.dropped()
+    assert (k["dropped_decode"], k["dropped_enum"]) == (d["decode"], d["enum"])
+
+
 @pytest.mark.parametrize("payload_bytes,hint", [(100, 100), (160, 160), (300, 300), (160, 0)])
 def test_larger_messages_windowed(payload_bytes, hint):
     spec = SynthSpec(n_keys=500, rate_per_ms=10, payload_bytes=payload_bytes, value_f64=True, malformed_ppm=5000)
