@@ -117,6 +117,10 @@ int build_schema(const bh_config& cfg, DevSchema& S) {
   S.tag_status = S.fast_status < 16 ? (S.fast_status << 3) : 0xFFFFFFFFu;
   S.tag_value = S.fast_value < 16 ? (S.fast_value << 3 | (S.fast_value_f64 ? 1u : 0u)) : 0xFFFFFFFFu;
   S.big_messages = cfg.message_bytes_hint > 72;
+  for (uint32_t n = 0; n < 16; n++) {
+    if (S.fld[n] == (uint32_t)BH_K_STRING) S.skip_str_mask |= 1u << n;
+    if (S.fld[n] == 0) S.skip_unk_mask |= 1u << n;
+  }
   S.n_parts = parts;
   S.mode = cfg.mode;
   if (cfg.mode == BH_MODE_REFERENCE) {

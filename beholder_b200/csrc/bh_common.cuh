@@ -113,6 +113,8 @@ struct DevSchema {
   uint32_t fast_value_f64;   // ... and it is a double
   uint32_t tag_key0, tag_status, tag_value;   // their canonical one-byte tags (0xFFFFFFFF = none)
   uint32_t big_messages;     // messages above ~72 B expected: kernels that stage a batch in parts
+  // by field number 0..15 (one-byte tags): bit set = a `string` with no role / a field the schema does not know
+  uint32_t skip_str_mask, skip_unk_mask;
   Div64 wdiv;
   // array members through functions: the compile-time schema view (ProgressSchema) offers the same names
   __host__ __device__ __forceinline__ uint32_t field(uint32_t number) const { return fld[number]; }

@@ -290,7 +290,12 @@ __device__ __forceinline__ void sts32(uint32_t a, uint32_t v) { asm volatile("st
 // =========================================================================================
 // A warp's batch is staged in shared memory SKEWED: 4 bytes of padding after every 64, so that 32
 // lanes walking 64-byte messages in lock step hit 32 different banks (stride 17 words) instead of 2.
-__device__ __forceinline__ uint32_t skew(uint32_t a) { return a + ((a >> 6) << 2); }
+// shift + multiply-add: two instructions (the plain C form is turned into shift, mask, add)
+__device__ __forceinline__ uint32_t skew(uint32_t a) {
+  uint32_t r;
+  asm("{\n\t.reg .u32 t;\n\tshr.u32 t, %1, 6;\n\tmad.lo.u32 %0, t, 4, %1;\n\t}" : "=r"(r) : "r"(a));
+  return r;
+}
 
 struct SmemRd {           // event bytes staged (skewed) in shared memory
   // Positions are in the warp buffer's "origin space": the buffer's shared-window address is a multiple
@@ -563,6 +568,7 @@ struct ProgressSchema {
   static constexpr uint32_t n_parts = 2, identity_key = 0, status_part = 0, has_enum = 1, has_window = 1;
   static constexpr uint32_t int_values = 1, fast_key0 = 1, fast_status = 2, fast_status_part = 2, fast_value = 3;
   static constexpr uint32_t fast_value_f64 = 0, tag_key0 = 0x0A, tag_status = 0x10, tag_value = 0x18;
+  static constexpr uint32_t skip_str_mask = 1u << 4, skip_unk_mask = 0xFFFFu & ~0x1Eu;
   // run-time items
   uint32_t ops; uint64_t enum_mask, hash_seed; Div64 wdiv;
   __device__ __forceinline__ explicit ProgressSchema(const DevSchema& S)
@@ -577,7 +583,8 @@ bool progress_schema_matches(const DevSchema& S) {
          S.has_enum == P::has_enum && S.has_window == P::has_window && S.int_values == P::int_values &&
          S.fast_key0 == P::fast_key0 && S.fast_status == P::fast_status && S.fast_status_part == P::fast_status_part &&
          S.fast_value == P::fast_value && S.fast_value_f64 == P::fast_value_f64 && S.tag_key0 == P::tag_key0 &&
-         S.tag_status == P::tag_status && S.tag_value == P::tag_value && S.mode == BH_MODE_WINDOWED;
+         S.tag_status == P::tag_status && S.tag_value == P::tag_value && S.skip_str_mask == P::skip_str_mask &&
+         S.skip_unk_mask == P::skip_unk_mask && S.mode == BH_MODE_WINDOWED;
 }
 
 template <class SC>
@@ -591,8 +598,8 @@ __device__ __forceinline__ bool decode_straight(const SC& S, const SmemRd& r, ui
   // role-less strings (clamped) and unknown length-delimited fields (strict): skipped wherever they stand
   auto skip_plain = [&]() {
     while (ok && lp < end) {
-      const uint32_t f = (t & 0x80u) ? 0xFFFFu : S.field(t >> 3);
-      const bool str = f == (uint32_t)BH_K_STRING, unk = f == 0u && (t & 7u) == 2u;
+      // one-byte tags only: the masks have no bit above field 15, so a tag with the continuation bit matches neither
+      const bool str = (S.skip_str_mask >> (t >> 3)) & 1u, unk = ((S.skip_unk_mask >> (t >> 3)) & 1u) && (t & 7u) == 2u;
       if (!(str || unk)) break;                            // a field with a role (or anything unusual): caller decides
       if (lp + 2 > end) { ok = false; break; }
       lp += 2;
