@@ -9,7 +9,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libbeholder_gpu.so")
+# BEHOLDER_GPU_LIB: another build of the same library (A/B timing of kernel changes); default = the in-tree build
+LIB_PATH = os.environ.get("BEHOLDER_GPU_LIB") or os.path.join(_HERE, "libbeholder_gpu.so")
 
 BH_MAX_FIELDS = 16
 BH_MAX_ENUM = 64

@@ -12,9 +12,11 @@ ap.add_argument("--f64", action="store_true"); ap.add_argument("--zipf", action=
 ap.add_argument("--keys", type=int, default=1000); ap.add_argument("--events", type=int, default=12_500_000)
 ap.add_argument("--payload", type=int, default=64); ap.add_argument("--cap", type=int, default=2048)
 ap.add_argument("--hist", action="store_true"); ap.add_argument("--reps", type=int, default=10)
+ap.add_argument("--unknown-ppm", type=int, default=0); ap.add_argument("--malformed-ppm", type=int, default=0)
 a = ap.parse_args()
 n = a.events
-spec = SynthSpec(n_keys=a.keys, rate_per_ms=500, value_f64=a.f64, zipf=a.zipf, payload_bytes=a.payload)
+spec = SynthSpec(n_keys=a.keys, rate_per_ms=500, value_f64=a.f64, zipf=a.zipf, payload_bytes=a.payload,
+                 unknown_enum_ppm=a.unknown_ppm, malformed_ppm=a.malformed_ppm)
 p, o, t, total = generate_device(spec, 0, n)
 kh, ts, val = columns_device(spec, 0xBE401DE5, 0, n)
 ops = L.OP_COUNT | L.OP_SUM | L.OP_MIN | L.OP_MAX | (L.OP_HIST if a.hist else 0)
