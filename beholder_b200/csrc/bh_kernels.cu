@@ -626,17 +626,24 @@ __device__ __forceinline__ bool decode_straight(const SC& S, const SmemRd& r, ui
   __syncwarp(mask);
   skip_plain();
   __syncwarp(mask);
+  // status and integer value: one- or two-byte varints (longer ones are left to the slower tiers)
+  auto varint12 = [&](uint32_t& out) {
+    if (lp + 2 > end) { ok = false; return; }
+    if (!(n & 0x80u)) { out = n; lp += 2; return; }
+    const uint32_t b2 = r.ab(lp + 2);
+    if (lp + 3 > end || (b2 & 0x80u)) { ok = false; return; }
+    out = (n & 0x7Fu) | (b2 << 7); lp += 3;
+  };
   if (ok && lp < end && t == S.tag_status) {
-    if (lp + 2 > end || (n & 0x80u)) ok = false;
-    else { status = n; lp += 2; t = r.ab(lp); n = r.ab(lp + 1); }
+    varint12(status);
+    t = r.ab(lp); n = r.ab(lp + 1);
   }
   if (ok && lp < end && t == S.tag_value) {
     if (S.fast_value_f64) {
       if (lp + 9 > end) ok = false;
       else { value = __longlong_as_double((long long)r.le64(lp + 1 - r.off, 8)); lp += 9; }
     } else {
-      if (lp + 2 > end || (n & 0x80u)) ok = false;
-      else { uval = n; lp += 2; }
+      varint12(uval);
     }
     t = r.ab(lp); n = r.ab(lp + 1);
   }
