@@ -37,7 +37,7 @@ STATUS_NAMES = {
 K_STRING, K_BYTES, K_INT32, K_UINT32, K_SINT32, K_BOOL, K_FLOAT, K_DOUBLE = range(1, 9)
 R_KEY, R_STATUS, R_VALUE = 1, 2, 4
 OP_COUNT, OP_SUM, OP_MIN, OP_MAX, OP_HIST = 1, 2, 4, 8, 16
-F_GENERIC_KERNELS = 1   # bh_config.flags
+F_GENERIC_KERNELS, F_NO_NUMA_BIND = 1, 2   # bh_config.flags
 MODE_REFERENCE, MODE_WINDOWED = 0, 1
 EV_OK, EV_DROP_DECODE, EV_DROP_ENUM, EV_DROP_NAN = 0, 1, 2, 3
 

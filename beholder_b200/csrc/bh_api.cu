@@ -3,6 +3,10 @@
 #include <stdarg.h>
 #include <stdio.h>
 #include <stdlib.h>
+#include <ctype.h>
+#ifdef __linux__
+#include <sched.h>
+#endif
 
 #include <algorithm>
 #include <string>
@@ -220,6 +224,54 @@ struct DeviceGuard {
   ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
 };
 
+// Pinned host memory is placed on the NUMA node of the thread that allocates it.  While this guard lives,
+// the calling thread may only run on the CPUs of the GPU's own node, so that the ingest ring (and buffers
+// from bh_host_alloc) sit next to the PCIe root the copies go through: with 8 GPUs on two sockets the
+// other placement sends half of the H2D traffic over the socket interconnect.  Best effort: no sysfs
+// entry, a cpuset that excludes those CPUs, or BEHOLDER_NO_NUMA_BIND=1 leave the thread where it is.
+struct NumaLocalGuard {
+#ifdef __linux__
+  cpu_set_t old; bool bound = false;
+  explicit NumaLocalGuard(int device, bool enabled = true) {
+    const char* off = getenv("BEHOLDER_NO_NUMA_BIND");
+    if (!enabled || (off && off[0] == '1')) return;
+    char bus[32] = {0};
+    if (cudaDeviceGetPCIBusId(bus, sizeof bus, device) != cudaSuccess) { cudaGetLastError(); return; }
+    for (char* q = bus; *q; q++) *q = (char)tolower(*q);
+    char path[128];
+    snprintf(path, sizeof path, "/sys/bus/pci/devices/%s/numa_node", bus);
+    FILE* f = fopen(path, "r");
+    if (!f) return;
+    int node = -1;
+    if (fscanf(f, "%d", &node) != 1) node = -1;
+    fclose(f);
+    if (node < 0) return;
+    snprintf(path, sizeof path, "/sys/devices/system/node/node%d/cpulist", node);
+    f = fopen(path, "r");
+    if (!f) return;
+    char list[4096] = {0};
+    if (!fgets(list, sizeof list, f)) list[0] = 0;
+    fclose(f);
+    if (sched_getaffinity(0, sizeof old, &old) != 0) return;
+    cpu_set_t want; CPU_ZERO(&want);
+    int n_want = 0;
+    for (char* q = list; *q;) {                      // "0-31,64-95"
+      char* e; long a = strtol(q, &e, 10);
+      if (e == q) break;
+      long b = a;
+      if (*e == '-') { q = e + 1; b = strtol(q, &e, 10); }
+      for (long c = a; c <= b && c < CPU_SETSIZE; c++) if (CPU_ISSET((int)c, &old)) { CPU_SET((int)c, &want); n_want++; }
+      q = (*e == ',') ? e + 1 : e;
+      if (*e != ',') break;
+    }
+    if (n_want && sched_setaffinity(0, sizeof want, &want) == 0) bound = true;
+  }
+  ~NumaLocalGuard() { if (bound) sched_setaffinity(0, sizeof old, &old); }
+#else
+  explicit NumaLocalGuard(int, bool = true) {}
+#endif
+};
+
 int counters_status(const bh_counters& k) {
   if (k.dropped_table_full) return BH_ERR_TABLE_FULL;
   if (k.dropped_window) return BH_ERR_WINDOW_RING;
@@ -296,9 +348,12 @@ int bh_create(const bh_config* cfg, bh_ctx** out) {
   if (c->slab_bytes > 0xFFFFFF00ull) { fail(c, BH_ERR_INVALID, "slab_bytes must stay below 4 GiB (u32 offsets)"); return bail(BH_ERR_INVALID); }
   uint32_t n_slabs = cfg->n_slabs ? cfg->n_slabs : 3;
   c->slabs.resize(n_slabs);
-  for (auto& s : c->slabs) {
-    int r2 = slab_alloc(c, s);
-    if (r2) return bail(r2);
+  {
+    NumaLocalGuard numa(c->device, !(cfg->flags & BH_F_NO_NUMA_BIND));   // pinned ring on the GPU's NUMA node
+    for (auto& s : c->slabs) {
+      int r2 = slab_alloc(c, s);
+      if (r2) return bail(r2);
+    }
   }
   CUB_(cudaStreamSynchronize(c->st_compute));
 #undef CUB_
@@ -328,6 +383,9 @@ void bh_destroy(bh_ctx* c) {
 
 int bh_host_alloc(void** out, size_t bytes) {
   if (!out) return BH_ERR_INVALID;
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) { cudaGetLastError(); dev = 0; }
+  NumaLocalGuard numa(dev);          // on the current device's NUMA node
   cudaError_t e = cudaHostAlloc(out, bytes, cudaHostAllocPortable);
   if (e != cudaSuccess) { g_create_error = cudaGetErrorString(e); cudaGetLastError(); return e == cudaErrorMemoryAllocation ? BH_ERR_NOMEM : BH_ERR_CUDA; }
   return BH_OK;

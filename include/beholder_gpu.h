@@ -87,9 +87,12 @@ typedef struct bh_config {
 
 /* bh_config.flags */
 enum {
-  BH_F_GENERIC_KERNELS = 1     /* never launch the fused kernel that has the reference's own schema compiled in
+  BH_F_GENERIC_KERNELS = 1,    /* never launch the fused kernel that has the reference's own schema compiled in
                                 * (api.TelemetryProgress keyed by mediaId + status, int32 progress): same results,
                                 * slower; for tests.  The environment variable BEHOLDER_GENERIC_KERNELS=1 does the same. */
+  BH_F_NO_NUMA_BIND = 2        /* by default the pinned ingest ring (and bh_host_alloc buffers) are allocated while the
+                                * calling thread is confined to the CPUs of the GPU's NUMA node, and the thread's
+                                * affinity is restored afterwards; this flag (or BEHOLDER_NO_NUMA_BIND=1) turns it off */
 };
 
 /* One aggregate row.  REFERENCE mode: key_hash = status number, window_id = 0, count = the value of
