@@ -318,10 +318,17 @@ struct SmemRd {           // event bytes staged (skewed) in shared memory
 struct GmemRd {           // slow path: event parsed straight from global memory
   const uint8_t* p;
   __device__ __forceinline__ uint32_t b(uint32_t i) const { return __ldg(p + i); }
+  // up to 8 bytes from i, as one or two aligned 64-bit loads.  Only words that hold a wanted byte are
+  // read, so the last access ends at most 7 bytes after the message: inside the buffer's 16-byte round-up.
   __device__ __forceinline__ uint64_t le64(uint32_t i, uint32_t nvalid) const {
-    uint64_t w = 0;
-    for (uint32_t j = 0; j < 8 && j < nvalid; j++) w |= (uint64_t)__ldg(p + i + j) << (8 * j);
-    return w;
+    if (nvalid == 0) return 0ull;
+    if (nvalid > 8) nvalid = 8;
+    const uintptr_t q = (uintptr_t)(p + i);
+    const unsigned long long* a = (const unsigned long long*)(q & ~(uintptr_t)7);
+    const uint32_t sh = (uint32_t)(q & 7u) * 8u;
+    uint64_t w = __ldg(a) >> sh;
+    if (sh + 8u * nvalid > 64u) w |= (uint64_t)__ldg(a + 1) << (64u - sh);
+    return nvalid >= 8 ? w : (w & ((1ull << (8 * nvalid)) - 1));
   }
 };
 
