@@ -58,6 +58,30 @@ module.exports = function beholderGpu (cfg) {
       }
     },
     commit () { ackUpTo(native.flush(ctx)) },
+    // Raw-socket ingest (SURVEY section 8 f1): instead of amqp.listen + one rmsg per delivery, hand the tap
+    // every chunk the broker socket emits.  Bodies go to the GPU ring in one batch per chunk; `ack` is the
+    // batched form of index.js:154 -- one basic.ack with allUpTo for everything the GPU has committed.
+    //   const tap = gpu.amqpTap({ consumerTag, channel })        // channel: an amqplib Channel
+    //   socket.on('data', chunk => tap.onData(chunk))
+    amqpTap ({ consumerTag, channel }) {
+      const tap = native.amqpCreate(consumerTag || '')
+      let rest = Buffer.alloc(0)
+      let lastTag = 0n
+      let acked = 0n
+      return {
+        onData (chunk) {
+          const buf = rest.length ? Buffer.concat([rest, chunk]) : chunk
+          const { consumed, tags } = native.amqpFeed(tap, ctx, buf, Date.now())
+          rest = buf.subarray(consumed)
+          if (tags.length) lastTag = tags[tags.length - 1]
+        },
+        // call on a timer or every N chunks: everything pushed so far is aggregated after flush()
+        ackCommitted () {
+          native.flush(ctx)
+          if (lastTag > acked) { channel.ack({ fields: { deliveryTag: Number(lastTag) } }, true); acked = lastTag }
+        }
+      }
+    },
     // { '<lower-cased enum name>': count } — the values of beholder_progress_updates_total{status=...}
     statusCounts () {
       api.commit()

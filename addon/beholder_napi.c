@@ -114,6 +114,68 @@ static napi_value Counters(napi_env env, napi_callback_info info) {
   return buf;
 }
 
+/* ---- AMQP 0-9-1 delivery tap (bh_amqp_*): socket bytes in, bodies pushed as one batch, tags out ----
+ * amqpCreate(consumerTag) -> external;  amqpFeed(tap, ctx, chunk: Buffer, tsMs) ->
+ *   { consumed: Number, tags: BigUint64Array }   (bodies of the deliveries completed inside `chunk`
+ * are already in the ingest ring when it returns; the caller keeps chunk.slice(consumed) for the next read) */
+#define TAP_SLAB (4u << 20)
+#define TAP_CAP 65536u
+typedef struct tap_box { bh_amqp* tap; uint8_t* slab; uint32_t* offsets; bh_amqp_delivery* del; } tap_box;
+
+static void tap_finalize(napi_env env, void* data, void* hint) {
+  tap_box* b = (tap_box*)data;
+  bh_amqp_destroy(b->tap); free(b->slab); free(b->offsets); free(b->del); free(b);
+}
+
+static napi_value AmqpCreate(napi_env env, napi_callback_info info) {
+  size_t argc = 1; napi_value argv[1]; char tag[256] = {0}; size_t tl = 0;
+  NAPI_OK(napi_get_cb_info(env, info, &argc, argv, NULL, NULL));
+  if (argc) napi_get_value_string_utf8(env, argv[0], tag, sizeof tag, &tl);
+  tap_box* b = (tap_box*)calloc(1, sizeof *b);
+  b->slab = (uint8_t*)malloc(TAP_SLAB); b->offsets = (uint32_t*)malloc((TAP_CAP + 1) * 4);
+  b->del = (bh_amqp_delivery*)malloc(TAP_CAP * sizeof(bh_amqp_delivery));
+  if (bh_amqp_create(&b->tap, tl ? tag : NULL, 0) != BH_OK) { napi_throw_error(env, NULL, "bh_amqp_create failed"); return NULL; }
+  napi_value ext;
+  NAPI_OK(napi_create_external(env, b, tap_finalize, NULL, &ext));
+  return ext;
+}
+
+static napi_value AmqpFeed(napi_env env, napi_callback_info info) {
+  size_t argc = 4; napi_value argv[4]; void* data; size_t len; int64_t ts = 0; tap_box* b;
+  NAPI_OK(napi_get_cb_info(env, info, &argc, argv, NULL, NULL));
+  NAPI_OK(napi_get_value_external(env, argv[0], (void**)&b));
+  bh_ctx* ctx = unwrap(env, argv[1]);
+  NAPI_OK(napi_get_buffer_info(env, argv[2], &data, &len));
+  NAPI_OK(napi_get_value_int64(env, argv[3], &ts));
+  uint64_t pos = 0, total = 0; size_t tcap = 1024; uint64_t* tags = (uint64_t*)malloc(tcap * 8);
+  for (;;) {
+    uint64_t used = 0; uint32_t n = 0;
+    int rc = bh_amqp_feed(b->tap, (const uint8_t*)data + pos, len - pos, b->slab, TAP_SLAB, b->offsets, b->del, TAP_CAP, &used, &n);
+    pos += used;
+    if (n) {   /* one timestamp for the batch: the arrival time of the socket read */
+      uint64_t* tsv = (uint64_t*)malloc((size_t)n * 8);
+      for (uint32_t i = 0; i < n; i++) tsv[i] = (uint64_t)ts;
+      int r2 = bh_push_batch(ctx, b->slab, b->offsets, tsv, n);
+      free(tsv);
+      if (r2 != BH_OK) { free(tags); return throw_bh(env, ctx, r2); }
+      if (total + n > tcap) { while (total + n > tcap) tcap *= 2; tags = (uint64_t*)realloc(tags, tcap * 8); }
+      for (uint32_t i = 0; i < n; i++) tags[total + i] = b->del[i].delivery_tag;
+      total += n;
+    }
+    if (rc != BH_OK) { free(tags); napi_throw_error(env, NULL, bh_amqp_last_error(b->tap)); return NULL; }
+    if (!n || !used) break;
+  }
+  napi_value res, cv, ab, ta; void* abdata;
+  NAPI_OK(napi_create_object(env, &res));
+  NAPI_OK(napi_create_double(env, (double)pos, &cv));
+  NAPI_OK(napi_create_arraybuffer(env, total * 8, &abdata, &ab));
+  memcpy(abdata, tags, total * 8); free(tags);
+  NAPI_OK(napi_create_typedarray(env, napi_biguint64_array, total, ab, 0, &ta));
+  NAPI_OK(napi_set_named_property(env, res, "consumed", cv));
+  NAPI_OK(napi_set_named_property(env, res, "tags", ta));
+  return res;
+}
+
 static napi_value Init(napi_env env, napi_value exports) {
   napi_property_descriptor props[] = {
     {"create", NULL, Create, NULL, NULL, NULL, napi_default, NULL},
@@ -122,6 +184,8 @@ static napi_value Init(napi_env env, napi_value exports) {
     {"poll", NULL, Poll, NULL, NULL, NULL, napi_default, NULL},
     {"snapshot", NULL, Snapshot, NULL, NULL, NULL, napi_default, NULL},
     {"counters", NULL, Counters, NULL, NULL, NULL, napi_default, NULL},
+    {"amqpCreate", NULL, AmqpCreate, NULL, NULL, NULL, napi_default, NULL},
+    {"amqpFeed", NULL, AmqpFeed, NULL, NULL, NULL, napi_default, NULL},
   };
   napi_define_properties(env, exports, sizeof props / sizeof props[0], props);
   return exports;

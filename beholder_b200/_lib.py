@@ -116,6 +116,26 @@ PROTOTYPES = {
                                           _u64p, _u64p, _u64p, _f64p, C.c_void_p]),
 }
 
+
+
+class BhAmqpDelivery(C.Structure):
+    _fields_ = [("delivery_tag", C.c_uint64), ("body_bytes", C.c_uint32), ("channel", C.c_uint16), ("redelivered", C.c_uint16)]
+
+
+class BhAmqpStats(C.Structure):
+    _fields_ = [(n, C.c_uint64) for n in ("frames", "deliveries", "body_bytes", "heartbeats", "other_methods",
+                                          "skipped_content", "filtered")]
+
+
+PROTOTYPES.update({
+    "bh_amqp_create": (C.c_int, [C.POINTER(C.c_void_p), C.c_char_p, C.c_uint64]),
+    "bh_amqp_destroy": (None, [C.c_void_p]),
+    "bh_amqp_feed": (C.c_int, [C.c_void_p, _u8p, C.c_uint64, _u8p, C.c_uint64, _u32p, C.POINTER(BhAmqpDelivery), C.c_uint32,
+                               C.POINTER(C.c_uint64), C.POINTER(C.c_uint32)]),
+    "bh_amqp_get_stats": (C.c_int, [C.c_void_p, C.POINTER(BhAmqpStats)]),
+    "bh_amqp_last_error": (C.c_char_p, [C.c_void_p]),
+})
+
 # test hooks that are not part of the public header
 _EXTRA = {"bh_debug_div64": (C.c_uint64, [C.c_uint64, C.c_uint64])}
 

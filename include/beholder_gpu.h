@@ -238,6 +238,48 @@ int bh_synth_columns_device(int device, const bh_synth_config* c, uint64_t hash_
                             uint64_t n, const uint64_t* d_zipf_cdf, uint64_t* d_key_hash,
                             uint64_t* d_ts, double* d_value, void* stream);
 
+/* ---------------------------------------------------------------------------------------------------
+ * AMQP 0-9-1 delivery tap.  Replaces, for the progress queue, what happens between
+ * the broker socket and the handler of index.js:127: amqplib 0.5.5 (yarn.lock:104-121, not vendored) parses
+ * frames, builds one message object per delivery and triton-core calls `fn(rmsg)`; here the raw
+ * broker -> client bytes of one connection are scanned once and the bodies of `basic.deliver` messages
+ * land in a slab + offsets pair that bh_push_batch / bh_push_batch_pinned take as is -- no per-message
+ * object.  Host code only (no GPU needed); frame grammar from the published AMQP 0-9-1 specification:
+ *   frame   = type:u8 channel:u16 size:u32 payload[size] 0xCE          (integers big-endian)
+ *   METHOD (1): class:u16 method:u16 args;  basic.deliver = (60,60): consumer-tag shortstr,
+ *               delivery-tag u64, redelivered octet, exchange shortstr, routing-key shortstr
+ *   HEADER (2): class:u16 weight:u16 body-size:u64 property flags/values
+ *   BODY   (3): body bytes (a message's body may span several frames)      HEARTBEAT (8): empty
+ * Content of basic.return (60,50) and basic.get-ok (60,71) is skipped; every other method and
+ * heartbeats are skipped and counted.  The tap never answers the broker: acks stay with the AMQP
+ * client, which uses the delivery tags reported here once bh_poll_committed has passed the batch
+ * (`channel.ack({fields:{deliveryTag}}, allUpTo = true)`, the batched form of index.js:154). */
+typedef struct bh_amqp bh_amqp;
+typedef struct bh_amqp_delivery {
+  uint64_t delivery_tag;
+  uint32_t body_bytes;
+  uint16_t channel;
+  uint16_t redelivered;
+} bh_amqp_delivery;
+typedef struct bh_amqp_stats {
+  uint64_t frames, deliveries, body_bytes, heartbeats, other_methods, skipped_content, filtered;
+} bh_amqp_stats;
+/* consumer_tag: only deliveries with this consumer tag are reported (NULL or "" = all of them);
+ * max_body: a larger announced body size is a protocol error (0 = 16 MiB) */
+int bh_amqp_create(bh_amqp** out, const char* consumer_tag, uint64_t max_body);
+void bh_amqp_destroy(bh_amqp* a);
+/* Scan bytes[0, len).  Whole frames are consumed; *consumed is where the caller's next call must start
+ * (an incomplete frame at the end is left; partly received messages are remembered inside `a`).
+ * Each completed delivery i gets deliveries[i] and its body at slab[offsets[i], offsets[i+1]);
+ * offsets[0] = 0, offsets has room for cap + 1 entries.  The scan stops early, before the frame that
+ * completes a message, when that message would not fit (slab_cap bytes, cap messages): flush what was
+ * returned and call again.  BH_ERR_INVALID = protocol error (bad frame end, unknown frame type, content
+ * without a method, body larger than announced): the connection must be dropped, as amqplib does. */
+int bh_amqp_feed(bh_amqp* a, const uint8_t* bytes, uint64_t len, uint8_t* slab, uint64_t slab_cap,
+                 uint32_t* offsets, bh_amqp_delivery* deliveries, uint32_t cap, uint64_t* consumed, uint32_t* n);
+int bh_amqp_get_stats(const bh_amqp* a, bh_amqp_stats* out);
+const char* bh_amqp_last_error(const bh_amqp* a);
+
 #ifdef __cplusplus
 }
 #endif
