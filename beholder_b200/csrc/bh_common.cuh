@@ -18,8 +18,16 @@ namespace bh {
 constexpr uint64_t kHashInit = 0x6A09E667F3BCC908ull;
 constexpr uint64_t kHashMul = 0x9E3779B97F4A7C15ull;
 
+// One word into the state: xor, fold the high half onto the low half, multiply, swap halves.  The fold
+// matters: a bit that sits at position 63 when the product is formed changes nothing but bit 63, so
+// without it two keys differing in bit 63 of one word and bit 31 of the next cancelled out exactly
+// (found by tests/test_gpu_fuzz.py with two flipped bits).  Folded, every input bit also enters the
+// product at a position <= 31 and spreads over at least the upper 32 bits before the next word arrives.
+// Each step stays a bijection of the state.
 BH_HD uint64_t absorb(uint64_t h, uint64_t w) {
-  h = (h ^ w) * kHashMul;
+  h ^= w;
+  h ^= h >> 32;
+  h *= kHashMul;
   return (h >> 32) | (h << 32);
 }
 BH_HD uint64_t fmix64(uint64_t h) {

@@ -271,8 +271,11 @@ static inline uint64_t fmix64(uint64_t h) {
   h ^= h >> 33; h *= 0xFF51AFD7ED558CCDull; h ^= h >> 33; h *= 0xC4CEB9FE1A85EC53ull; h ^= h >> 33;
   return h;
 }
+/* xor, fold high half onto low half, multiply, swap halves (BASELINE.md B.2 "Key") */
 static inline uint64_t absorb(uint64_t h, uint64_t w) {
-  h = (h ^ w) * 0x9E3779B97F4A7C15ull;
+  h ^= w;
+  h ^= h >> 32;
+  h *= 0x9E3779B97F4A7C15ull;
   return (h >> 32) | (h << 32);
 }
 static uint64_t absorb_bytes(uint64_t h, const uint8_t* p, uint32_t len, uint32_t field) {

@@ -85,3 +85,33 @@ def test_key_hash_has_no_collisions_on_many_uuid_keys():
     # low bits and high bits both spread (table index uses high bits of kh * phi; owner uses top bits)
     assert len(np.unique(recs["key_hash"] >> np.uint64(56))) == 256
     assert len(np.unique(recs["key_hash"] & np.uint64(0xFF))) == 256
+
+
+def test_key_hash_separates_keys_that_differ_in_a_few_chosen_bits():
+    """The first version of the hash multiplied without folding the high half down: a flipped bit 63 of
+    one 8-byte word and a flipped bit 31 of the next cancelled exactly.  Every pair of 36-byte keys that
+    differs in one or two bits must hash apart (all 288 single flips, every pair of flips that involves
+    a word's top bit, and 20 000 random pairs)."""
+    import ctypes as C
+    rng = np.random.default_rng(SEED)
+    base = bytearray(b"d418035b-9722-015d-8d9a-e76ed8cd1872")
+    nbits = len(base) * 8
+
+    def h(b):
+        buf = (C.c_uint8 * len(b)).from_buffer_copy(bytes(b))
+        return O.lib.bho_hash_bytes(C.addressof(buf), len(b), 1, SEED)
+
+    def flipped(*bits):
+        b = bytearray(base)
+        for i in bits:
+            b[i // 8] ^= 1 << (i % 8)
+        return b
+
+    seen = {h(base): ()}
+    pairs = [(i,) for i in range(nbits)]
+    pairs += [(i, j) for i in range(63, nbits, 64) for j in range(nbits) if j != i]     # a word's top bit + any other bit
+    pairs += [tuple(sorted(rng.choice(nbits, 2, replace=False).tolist())) for _ in range(20000)]
+    for p in set(pairs):
+        v = h(flipped(*p))
+        assert v not in seen, (p, seen[v])
+        seen[v] = p
