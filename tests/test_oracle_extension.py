@@ -111,7 +111,7 @@ def test_key_hash_separates_keys_that_differ_in_a_few_chosen_bits():
     pairs = [(i,) for i in range(nbits)]
     pairs += [(i, j) for i in range(63, nbits, 64) for j in range(nbits) if j != i]     # a word's top bit + any other bit
     pairs += [tuple(sorted(rng.choice(nbits, 2, replace=False).tolist())) for _ in range(20000)]
-    for p in set(pairs):
+    for p in {tuple(sorted(q)) for q in pairs}:
         v = h(flipped(*p))
         assert v not in seen, (p, seen[v])
         seen[v] = p
