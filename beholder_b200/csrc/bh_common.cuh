@@ -18,17 +18,20 @@ namespace bh {
 constexpr uint64_t kHashInit = 0x6A09E667F3BCC908ull;
 constexpr uint64_t kHashMul = 0x9E3779B97F4A7C15ull;
 
-// One word into the state: xor, fold the high half onto the low half, multiply, swap halves.  The fold
-// matters: a bit that sits at position 63 when the product is formed changes nothing but bit 63, so
-// without it two keys differing in bit 63 of one word and bit 31 of the next cancelled out exactly
-// (found by tests/test_gpu_fuzz.py with two flipped bits).  Folded, every input bit also enters the
-// product at a position <= 31 and spreads over at least the upper 32 bits before the next word arrives.
-// Each step stays a bijection of the state.
+// One word into the state: xor, 64-bit multiply, then a second, 32-bit multiply of the product's low half
+// mixed with its high half rotated by 16, halves swapped.  Why two multiplies: a bit that sits at
+// position 63 when a product is formed changes nothing but bit 63 of it, a fixed one-bit difference that
+// the NEXT word can cancel exactly.  The first version (one multiply + swap) let two keys differing in
+// bit 63 of one word and bit 31 of the next collide; folding the halves before the multiply only moved
+// the pattern to three bits (both found by tests: test_gpu_fuzz.py, test_oracle_extension.py).  Here the
+// product's top bit enters the second multiply at bit 15, so every input difference has become a
+// data-dependent many-bit difference before the next word arrives.  Each step is a bijection of the state.
+constexpr uint32_t kHashMul32 = 0x85EBCA6Bu;
 BH_HD uint64_t absorb(uint64_t h, uint64_t w) {
-  h ^= w;
-  h ^= h >> 32;
-  h *= kHashMul;
-  return (h >> 32) | (h << 32);
+  const uint64_t m = (h ^ w) * kHashMul;
+  const uint32_t hi = (uint32_t)(m >> 32);
+  const uint32_t lo = ((uint32_t)m ^ ((hi << 16) | (hi >> 16))) * kHashMul32;
+  return ((uint64_t)lo << 32) | hi;
 }
 BH_HD uint64_t fmix64(uint64_t h) {
   h ^= h >> 33; h *= 0xFF51AFD7ED558CCDull; h ^= h >> 33; h *= 0xC4CEB9FE1A85EC53ull; h ^= h >> 33;

@@ -271,12 +271,12 @@ static inline uint64_t fmix64(uint64_t h) {
   h ^= h >> 33; h *= 0xFF51AFD7ED558CCDull; h ^= h >> 33; h *= 0xC4CEB9FE1A85EC53ull; h ^= h >> 33;
   return h;
 }
-/* xor, fold high half onto low half, multiply, swap halves (BASELINE.md B.2 "Key") */
+/* BASELINE.md B.2 "Key": xor, 64-bit multiply, 32-bit multiply of (low half ^ rot16(high half)), swap halves */
 static inline uint64_t absorb(uint64_t h, uint64_t w) {
-  h ^= w;
-  h ^= h >> 32;
-  h *= 0x9E3779B97F4A7C15ull;
-  return (h >> 32) | (h << 32);
+  uint64_t m = (h ^ w) * 0x9E3779B97F4A7C15ull;
+  uint32_t hi = (uint32_t)(m >> 32);
+  uint32_t lo = ((uint32_t)m ^ ((hi << 16) | (hi >> 16))) * 0x85EBCA6Bu;
+  return ((uint64_t)lo << 32) | hi;
 }
 static uint64_t absorb_bytes(uint64_t h, const uint8_t* p, uint32_t len, uint32_t field) {
   uint32_t i = 0;

@@ -88,11 +88,13 @@ def test_key_hash_has_no_collisions_on_many_uuid_keys():
 
 
 def test_key_hash_separates_keys_that_differ_in_a_few_chosen_bits():
-    """The first version of the hash multiplied without folding the high half down: a flipped bit 63 of
-    one 8-byte word and a flipped bit 31 of the next cancelled exactly.  Every pair of 36-byte keys that
-    differs in one or two bits must hash apart (all 288 single flips, every pair of flips that involves
-    a word's top bit, and 20 000 random pairs)."""
+    """A multiply leaves a difference in bit 63 of its operand as a difference in bit 63 only, which the next
+    8-byte word can cancel.  Earlier versions of the hash collided on keys differing in {bit 63 of word i,
+    bit 31 of word i+1} and then in three such bits.  All 36-byte keys within one, two or (for the bits a
+    multiply treats specially: 15, 31, 47, 63 of every word) three flipped bits of each other, plus 20 000
+    random flip sets of up to 6 bits, must hash apart."""
     import ctypes as C
+    import itertools
     rng = np.random.default_rng(SEED)
     base = bytearray(b"d418035b-9722-015d-8d9a-e76ed8cd1872")
     nbits = len(base) * 8
@@ -101,17 +103,22 @@ def test_key_hash_separates_keys_that_differ_in_a_few_chosen_bits():
         buf = (C.c_uint8 * len(b)).from_buffer_copy(bytes(b))
         return O.lib.bho_hash_bytes(C.addressof(buf), len(b), 1, SEED)
 
-    def flipped(*bits):
+    def flipped(bits):
         b = bytearray(base)
         for i in bits:
             b[i // 8] ^= 1 << (i % 8)
         return b
 
-    seen = {h(base): ()}
-    pairs = [(i,) for i in range(nbits)]
-    pairs += [(i, j) for i in range(63, nbits, 64) for j in range(nbits) if j != i]     # a word's top bit + any other bit
-    pairs += [tuple(sorted(rng.choice(nbits, 2, replace=False).tolist())) for _ in range(20000)]
-    for p in {tuple(sorted(q)) for q in pairs}:
-        v = h(flipped(*p))
+    sets = {()}
+    sets |= {(i,) for i in range(nbits)}
+    sets |= set(itertools.combinations(range(nbits), 2))
+    special = [w * 64 + b for w in range(nbits // 64 + 1) for b in (15, 31, 47, 63) if w * 64 + b < nbits]
+    sets |= set(itertools.combinations(special, 3))
+    for _ in range(20000):
+        k = int(rng.integers(3, 7))
+        sets.add(tuple(sorted(rng.choice(nbits, k, replace=False).tolist())))
+    seen = {}
+    for p in sets:
+        v = h(flipped(p))
         assert v not in seen, (p, seen[v])
         seen[v] = p
