@@ -594,6 +594,79 @@ bool progress_schema_matches(const DevSchema& S) {
          S.skip_unk_mask == P::skip_unk_mask && S.mode == BH_MODE_WINDOWED;
 }
 
+// Tier 0 of the decoder: the wire layout a writer produces when it serialises this message in field
+// order -- [key part 0 string, or a role-less string when the key has no string part] [one role-less
+// string / unknown length-delimited field] [status] [value] [one role-less string / unknown
+// length-delimited field], each optional, one-byte tags, one-byte status
+// and integer value, one- or two-byte string lengths.  Written without branches (every stage is a handful
+// of predicated instructions), so the lanes of a warp stay together; whatever does not fit is left,
+// untouched, to decode_straight and the tiers behind it.  Each stage applies exactly the tests
+// decode_straight applies to the same bytes.
+template <class SC>
+__device__ __forceinline__ bool decode_canon(const SC& S, const SmemRd& r, uint32_t len, Parsed& P) {
+  uint32_t lp = r.off;
+  const uint32_t end = lp + len;
+  uint32_t t = r.ab(lp), n = r.ab(lp + 1);
+  bool ok = true;
+  uint32_t kpos = 0, klen = 0, status = 0, uval = 0;
+  double value = 0.0;
+  // one optional role-less string (clamped to the end) or unknown length-delimited field (strict)
+  auto plain = [&]() {
+    const bool str = (S.skip_str_mask >> (t >> 3)) & 1u, unk = ((S.skip_unk_mask >> (t >> 3)) & 1u) && (t & 7u) == 2u;
+    const bool here = ok && lp < end && (str || unk);
+    const uint32_t b2 = r.ab(lp + 2);
+    const bool two = (n & 0x80u) != 0;
+    const bool good_len = lp + 2 <= end && (!two || (lp + 2 < end && !(b2 & 0x80u)));
+    const uint32_t ln = two ? ((n & 0x7Fu) | (b2 << 7)) : n;
+    const uint32_t after = lp + (two ? 3u : 2u) + ln;
+    const bool good = good_len && !(after > end && unk);     // string() clamps, skip() throws
+    ok = ok && (!here || good);
+    if (here && good) lp = min(after, end);
+  };
+  if (S.tag_key0 != 0xFFFFFFFFu) {                           // (uniform) the first field is key part 0 ...
+    const bool here = lp < end && t == S.tag_key0;
+    const bool good = lp + 2 <= end && !(n & 0x80u);
+    ok = !here || good;
+    if (here && good) {
+      const uint32_t e2 = min(lp + 2 + n, end);              // BufferReader.string() clamps
+      kpos = lp + 2 - r.off; klen = e2 - (lp + 2); lp = e2;
+    }
+  } else {                                                   // ... or, with no string key (reference mode), one more plain field
+    plain();
+  }
+  t = r.ab(lp); n = r.ab(lp + 1);
+  plain();
+  t = r.ab(lp); n = r.ab(lp + 1);
+  {
+    const bool here = ok && lp < end && t == S.tag_status;
+    const bool good = lp + 2 <= end && !(n & 0x80u);
+    ok = ok && (!here || good);
+    if (here && good) { status = n; lp += 2; }
+    t = r.ab(lp); n = r.ab(lp + 1);
+  }
+  {
+    const bool here = ok && lp < end && t == S.tag_value;
+    if (S.fast_value_f64) {
+      const bool good = lp + 9 <= end;
+      ok = ok && (!here || good);
+      if (here && good) { value = __longlong_as_double((long long)r.le64(lp + 1 - r.off, 8)); lp += 9; }
+    } else {
+      const bool good = lp + 2 <= end && !(n & 0x80u);
+      ok = ok && (!here || good);
+      if (here && good) { uval = n; lp += 2; }
+    }
+    t = r.ab(lp); n = r.ab(lp + 1);
+  }
+  plain();
+  ok = ok && lp == end;
+  P.clear();
+  P.ppos[0] = kpos; P.plen[0] = klen; P.status = status; P.uval = uval; P.value = value;
+  if (S.fast_status_part == 1) P.pval[0] = status;
+  if (S.fast_status_part == 2) P.pval[1] = status;
+  if (S.fast_status_part == 3) P.pval[2] = status;
+  return ok;
+}
+
 template <class SC>
 __device__ __forceinline__ bool decode_straight(const SC& S, const SmemRd& r, uint32_t len, Parsed& P, uint32_t mask) {
   uint32_t lp = r.off;
@@ -722,7 +795,13 @@ __device__ __forceinline__ uint32_t decode_and_check_smem(const SC& S, const Sme
                                                           double& value, int32_t& ival, uint32_t& status, uint32_t mask) {
   Parsed P;
   uint32_t slow = 0;
-  if (!decode_straight(S, r, len, P, mask)) {
+#ifdef BH_NO_TIER0
+  const bool canon = false;
+#else
+  const bool canon = decode_canon(S, r, len, P);
+#endif
+  const uint32_t rest = __ballot_sync(mask, !canon);      // the lanes that go on to the next tier, together
+  if (!canon && !decode_straight(S, r, len, P, rest)) {
     Parsed Q;   // a separate object: P must not escape into the out-of-line slow path (it would live in local memory)
     if (!decode_slow(S, r, len, Q)) { kh = 0; value = 0.0; ival = 0; status = 0; return BH_EV_DROP_DECODE | kSlowDecode; }
     P = Q;
