@@ -281,9 +281,32 @@ __device__ __forceinline__ void counters_flush(const DevTables& T, LaneCounters&
 }
 
 // shared-memory access by 32-bit shared-window address, for the staged payload bytes
-__device__ __forceinline__ uint32_t lds8(uint32_t a) { uint32_t v; asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(a)); return v; }
-__device__ __forceinline__ uint32_t lds32(uint32_t a) { uint32_t v; asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a)); return v; }
-__device__ __forceinline__ void sts32(uint32_t a, uint32_t v) { asm volatile("st.shared.u32 [%0], %1;" :: "r"(a), "r"(v) : "memory"); }
+// -DBH_BOUNDS_CHECK (debug builds; compute-sanitizer is not available on the test pool): every access to a
+// warp's staging buffer is checked against that buffer, every byte the global-memory reader touches
+// against the batch's readable range; a violation prints once and traps.
+#ifdef BH_BOUNDS_CHECK
+}  // namespace bh
+#include <stdio.h>
+namespace bh {
+__shared__ uint32_t g_dbg_first;                 // shared-window address where the warp buffers start
+__device__ const uint8_t* g_dbg_glo; __device__ const uint8_t* g_dbg_ghi;
+__device__ __forceinline__ void dbg_smem(uint32_t a, uint32_t bytes) {
+  const uint32_t lo = ((g_dbg_first + 67u) / 68u + (threadIdx.x >> 5) * 37u) * 68u, hi = lo + 37u * 68u;
+  if (a < lo || a + bytes > hi) { printf("warp-buffer access %u+%u outside [%u,%u) block %u thread %u\n", a, bytes, lo, hi, blockIdx.x, threadIdx.x); __trap(); }
+}
+__device__ __forceinline__ void dbg_gmem(const void* p, uint32_t bytes) {
+  const uint8_t* q = (const uint8_t*)p;
+  if (q < g_dbg_glo || q + bytes > g_dbg_ghi) { printf("global read %p+%u outside [%p,%p)\n", p, bytes, g_dbg_glo, g_dbg_ghi); __trap(); }
+}
+#define BH_DBG_SMEM(a, n) dbg_smem(a, n)
+#define BH_DBG_GMEM(p, n) dbg_gmem(p, n)
+#else
+#define BH_DBG_SMEM(a, n) ((void)0)
+#define BH_DBG_GMEM(p, n) ((void)0)
+#endif
+__device__ __forceinline__ uint32_t lds8(uint32_t a) { BH_DBG_SMEM(a, 1); uint32_t v; asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(a)); return v; }
+__device__ __forceinline__ uint32_t lds32(uint32_t a) { BH_DBG_SMEM(a, 4); uint32_t v; asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a)); return v; }
+__device__ __forceinline__ void sts32(uint32_t a, uint32_t v) { BH_DBG_SMEM(a, 4); asm volatile("st.shared.u32 [%0], %1;" :: "r"(a), "r"(v) : "memory"); }
 
 // =========================================================================================
 // protobufjs 6.8.8 reader semantics on the device (what proto.decode does, index.js:129)
@@ -317,7 +340,7 @@ struct SmemRd {           // event bytes staged (skewed) in shared memory
 };
 struct GmemRd {           // slow path: event parsed straight from global memory
   const uint8_t* p;
-  __device__ __forceinline__ uint32_t b(uint32_t i) const { return __ldg(p + i); }
+  __device__ __forceinline__ uint32_t b(uint32_t i) const { BH_DBG_GMEM(p + i, 1); return __ldg(p + i); }
   // up to 8 bytes from i, as one or two aligned 64-bit loads.  Only words that hold a wanted byte are
   // read, so the last access ends at most 7 bytes after the message: inside the buffer's 16-byte round-up.
   __device__ __forceinline__ uint64_t le64(uint32_t i, uint32_t nvalid) const {
@@ -326,8 +349,9 @@ struct GmemRd {           // slow path: event parsed straight from global memory
     const uintptr_t q = (uintptr_t)(p + i);
     const unsigned long long* a = (const unsigned long long*)(q & ~(uintptr_t)7);
     const uint32_t sh = (uint32_t)(q & 7u) * 8u;
+    BH_DBG_GMEM(a, 8);
     uint64_t w = __ldg(a) >> sh;
-    if (sh + 8u * nvalid > 64u) w |= (uint64_t)__ldg(a + 1) << (64u - sh);
+    if (sh + 8u * nvalid > 64u) { BH_DBG_GMEM(a + 1, 8); w |= (uint64_t)__ldg(a + 1) << (64u - sh); }
     return nvalid >= 8 ? w : (w & ((1ull << (8 * nvalid)) - 1));
   }
 };
@@ -829,6 +853,7 @@ __device__ __noinline__ uint32_t decode_and_check_gmem(const DevSchema& S, const
 constexpr uint32_t kWarpBuf = 2304;                                  // payload bytes staged per warp batch (32 x 72)
 constexpr uint32_t kWarpChunks = (kWarpBuf / 16 + 1 + 31) / 32;      // 16-byte chunks per lane (5)
 constexpr uint32_t kWarpBufAlloc = ((kWarpBuf + kWarpBuf / 16 + 64 + 67) / 68) * 68;   // + skew padding + over-read slack, multiple of 68
+static_assert(kWarpBufAlloc == 37u * 68u, "BH_BOUNDS_CHECK hard-codes the buffer size");
 constexpr uint32_t kWarpBufSlack = 68;   // the first warp buffer is moved up to a multiple of 68
 
 // origin (see SmemRd) of the calling warp's buffer; `first` = shared-window address where warp buffers may start
@@ -987,6 +1012,12 @@ k_process_raw(const __grid_constant__ DevSchema S, const __grid_constant__ DevTa
                                          ((ns * smem_slot_bytes(INTV, hist) + 15u) & ~15u));
   smem_table_clear<INTV>(M);
   if (threadIdx.x < 8) g_cnt[threadIdx.x] = 0;
+#ifdef BH_BOUNDS_CHECK
+  if (threadIdx.x == 0) {
+    g_dbg_first = (uint32_t)__cvta_generic_to_shared(g_smem) + ((ns * smem_slot_bytes(INTV, hist) + 15u) & ~15u);
+    g_dbg_glo = payload; g_dbg_ghi = payload + ((offsets[n] + 15u) & ~15u);    // every CTA writes the same values
+  }
+#endif
   __syncthreads();
   const uint32_t cs = min(n, blockIdx.x * chunk), ce = min(n, cs + chunk);
   LaneCounters C{0u};
@@ -1024,6 +1055,13 @@ k_decode(const __grid_constant__ DevSchema S, const uint8_t* __restrict__ payloa
          const uint32_t* __restrict__ offsets, uint32_t n, uint32_t chunk, uint64_t* kh, double* val,
          int32_t* status, uint8_t* outcome) {
   const uint32_t wb = warp_buffer_origin((uint32_t)__cvta_generic_to_shared(g_smem));
+#ifdef BH_BOUNDS_CHECK
+  if (threadIdx.x == 0) {
+    g_dbg_first = (uint32_t)__cvta_generic_to_shared(g_smem);
+    g_dbg_glo = payload; g_dbg_ghi = payload + ((offsets[n] + 15u) & ~15u);
+  }
+  __syncthreads();
+#endif
   const uint32_t cs = min(n, blockIdx.x * chunk), ce = min(n, cs + chunk);
   if (cs >= ce) return;
   ColumnSink sink{S, kh, val, status, outcome};
