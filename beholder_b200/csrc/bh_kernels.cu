@@ -584,48 +584,50 @@ __device__ __forceinline__ bool decode_fast(const DevSchema& S, const SmemRd& r,
 // look-ups and tests; what varies at run time (ops, enum mask, hash seed, window divisor) still comes from the
 // DevSchema.  The host launches the kernel built on this view only when progress_schema_matches() says that
 // the run-time schema is exactly this one; every other schema runs the same code on the DevSchema itself.
-struct ProgressSchema {
+// REF = false: the windowed grouping above.  REF = true: the reference's literal counter (BH_MODE_REFERENCE:
+// key = status, no key parts, no windows; mediaId is just another string to skip).
+template <bool REF>
+struct ProgressSchemaT {
   const DevSchema& dyn;
   __device__ __forceinline__ operator const DevSchema&() const { return dyn; }
-  static constexpr uint32_t kFld1 = BH_K_STRING | (BH_R_KEY << 8) | (1u << 16);
-  static constexpr uint32_t kFld2 = BH_K_INT32 | ((BH_R_KEY | BH_R_STATUS) << 8) | (2u << 16);
+  static constexpr uint32_t kFld1 = REF ? (uint32_t)BH_K_STRING : (BH_K_STRING | (BH_R_KEY << 8) | (1u << 16));
+  static constexpr uint32_t kFld2 = REF ? (BH_K_INT32 | (BH_R_STATUS << 8)) : (BH_K_INT32 | ((BH_R_KEY | BH_R_STATUS) << 8) | (2u << 16));
   static constexpr uint32_t kFld3 = BH_K_INT32 | (BH_R_VALUE << 8);
   static constexpr uint32_t kFld4 = BH_K_STRING;
   __host__ __device__ static constexpr uint32_t field(uint32_t n) {
     return n == 1 ? kFld1 : n == 2 ? kFld2 : n == 3 ? kFld3 : n == 4 ? kFld4 : 0u;
   }
-  __host__ __device__ static constexpr uint32_t part_len(int k) { return k == 0 ? 1u : 0u; }
-  __host__ __device__ static constexpr uint32_t part_fld(int k) { return k == 0 ? 1u : k == 1 ? 2u : 0u; }
-  static constexpr uint32_t n_parts = 2, identity_key = 0, status_part = 0, has_enum = 1, has_window = 1;
-  static constexpr uint32_t int_values = 1, fast_key0 = 1, fast_status = 2, fast_status_part = 2, fast_value = 3;
-  static constexpr uint32_t fast_value_f64 = 0, tag_key0 = 0x0A, tag_status = 0x10, tag_value = 0x18;
-  static constexpr uint32_t skip_str_mask = 1u << 4, skip_unk_mask = 0xFFFFu & ~0x1Eu;
+  __host__ __device__ static constexpr uint32_t part_len(int k) { return !REF && k == 0 ? 1u : 0u; }
+  __host__ __device__ static constexpr uint32_t part_fld(int k) { return REF ? 0u : k == 0 ? 1u : k == 1 ? 2u : 0u; }
+  static constexpr uint32_t n_parts = REF ? 0 : 2, identity_key = 0, status_part = REF ? 1 : 0, has_enum = 1;
+  static constexpr uint32_t has_window = REF ? 0 : 1, mode = REF ? BH_MODE_REFERENCE : BH_MODE_WINDOWED;
+  static constexpr uint32_t int_values = 1, fast_key0 = REF ? 0xFFFFFFFFu : 1u, fast_status = 2;
+  static constexpr uint32_t fast_status_part = REF ? 0 : 2, fast_value = 3;
+  static constexpr uint32_t fast_value_f64 = 0, tag_key0 = REF ? 0xFFFFFFFFu : 0x0Au, tag_status = 0x10, tag_value = 0x18;
+  static constexpr uint32_t skip_str_mask = REF ? ((1u << 1) | (1u << 4)) : (1u << 4), skip_unk_mask = 0xFFFFu & ~0x1Eu;
   // run-time items
   uint32_t ops; uint64_t enum_mask, hash_seed; Div64 wdiv;
-  __device__ __forceinline__ explicit ProgressSchema(const DevSchema& S)
+  __device__ __forceinline__ explicit ProgressSchemaT(const DevSchema& S)
       : dyn(S), ops(S.ops), enum_mask(S.enum_mask), hash_seed(S.hash_seed), wdiv(S.wdiv) {}
 };
+typedef ProgressSchemaT<false> ProgressSchema;
 
-bool progress_schema_matches(const DevSchema& S) {
-  typedef ProgressSchema P;
+template <bool REF>
+static bool schema_matches(const DevSchema& S) {
+  typedef ProgressSchemaT<REF> P;
   for (uint32_t n = 0; n < 32; n++) if (S.fld[n] != P::field(n)) return false;
-  for (int k = 0; k < (int)P::n_parts; k++) if (S.part_is_len[k] != P::part_len(k) || S.part_field[k] != P::part_fld(k)) return false;
+  for (int k = 0; k < BH_MAX_KEY_PARTS; k++) if (S.part_is_len[k] != P::part_len(k) || S.part_field[k] != P::part_fld(k)) return false;
   return S.n_parts == P::n_parts && S.identity_key == P::identity_key && S.status_part == P::status_part &&
          S.has_enum == P::has_enum && S.has_window == P::has_window && S.int_values == P::int_values &&
          S.fast_key0 == P::fast_key0 && S.fast_status == P::fast_status && S.fast_status_part == P::fast_status_part &&
          S.fast_value == P::fast_value && S.fast_value_f64 == P::fast_value_f64 && S.tag_key0 == P::tag_key0 &&
          S.tag_status == P::tag_status && S.tag_value == P::tag_value && S.skip_str_mask == P::skip_str_mask &&
-         S.skip_unk_mask == P::skip_unk_mask && S.mode == BH_MODE_WINDOWED;
+         S.skip_unk_mask == P::skip_unk_mask && S.mode == P::mode;
 }
+// 0 = no compiled-in view fits, 1 = windowed (mediaId, status) grouping, 2 = reference mode
+int progress_schema_variant(const DevSchema& S) { return schema_matches<false>(S) ? 1 : schema_matches<true>(S) ? 2 : 0; }
+bool progress_schema_matches(const DevSchema& S) { return progress_schema_variant(S) != 0; }
 
-// Tier 0 of the decoder: the wire layout a writer produces when it serialises this message in field
-// order -- [key part 0 string, or a role-less string when the key has no string part] [one role-less
-// string / unknown length-delimited field] [status] [value] [one role-less string / unknown
-// length-delimited field], each optional, one-byte tags, one-byte status
-// and integer value, one- or two-byte string lengths.  Written without branches (every stage is a handful
-// of predicated instructions), so the lanes of a warp stay together; whatever does not fit is left,
-// untouched, to decode_straight and the tiers behind it.  Each stage applies exactly the tests
-// decode_straight applies to the same bytes.
 template <class SC>
 __device__ __forceinline__ bool decode_canon(const SC& S, const SmemRd& r, uint32_t len, Parsed& P) {
   uint32_t lp = r.off;
@@ -792,7 +794,7 @@ __device__ __forceinline__ uint64_t event_key_hash_smem(const SC& S, const SmemR
   uint64_t h = S.hash_seed ^ kHashInit;
 #pragma unroll
   for (int k = 0; k < BH_MAX_KEY_PARTS; k++) {
-    if ((uint32_t)k >= S.n_parts) break;
+    if (k >= (int)S.n_parts) break;
     if (S.part_len(k)) h = hash_span_smem(r, r.off + P.ppos[k], P.plen[k], S.part_fld(k), h);
     else h = absorb(h, varint_word(P.pval[k], S.part_fld(k)));
   }
@@ -1000,8 +1002,9 @@ __device__ __forceinline__ void process_chunk(const SC& S, const DevTables& T, c
   raw_warp_loop<BIG>(S, payload, offsets, cs, ce, wb, sink);
 }
 
-// PROG: the schema is the reference's own (ProgressSchema) and is read as compile-time constants
-template <bool INTV, bool BIG, bool PROG>
+// PROG != 0: the schema is the reference's own (ProgressSchemaT: 1 windowed grouping, 2 reference mode) and
+// is read as compile-time constants
+template <bool INTV, bool BIG, int PROG>
 __global__ void __launch_bounds__(INTV ? kRawThreads : kRawThreadsF64, 1)
 k_process_raw(const __grid_constant__ DevSchema S, const __grid_constant__ DevTables T,
               const uint8_t* __restrict__ payload, const uint32_t* __restrict__ offsets,
@@ -1023,8 +1026,8 @@ k_process_raw(const __grid_constant__ DevSchema S, const __grid_constant__ DevTa
   LaneCounters C{0u};
   uint64_t wbase = 0;
   if (cs < ce) {
-    if constexpr (PROG) {
-      const ProgressSchema PS(S);
+    if constexpr (PROG != 0) {
+      const ProgressSchemaT<PROG == 2> PS(S);
       process_chunk<INTV, BIG>(PS, T, M, payload, offsets, ts, cs, ce, wb, C, wbase);
     } else {
       process_chunk<INTV, BIG>(S, T, M, payload, offsets, ts, cs, ce, wb, C, wbase);
@@ -1224,9 +1227,9 @@ __global__ void k_close_release(const __grid_constant__ DevTables T, uint64_t wi
 // once per device, with that device current (bh_create)
 cudaError_t configure_kernels(const LaunchGeom& G) {
   int dyn = G.smem_optin - 1024;   // leave room for the kernels' static shared memory
-  const void* fns[] = {(const void*)k_process_raw<true, false, false>, (const void*)k_process_raw<true, true, false>,
-                       (const void*)k_process_raw<false, false, false>, (const void*)k_process_raw<false, true, false>,
-                       (const void*)k_process_raw<true, false, true>,
+  const void* fns[] = {(const void*)k_process_raw<true, false, 0>, (const void*)k_process_raw<true, true, 0>,
+                       (const void*)k_process_raw<false, false, 0>, (const void*)k_process_raw<false, true, 0>,
+                       (const void*)k_process_raw<true, false, 1>, (const void*)k_process_raw<true, false, 2>,
                        (const void*)k_decode<false>, (const void*)k_decode<true>, (const void*)k_process_columns};
   for (const void* f : fns) {
     cudaError_t e = cudaFuncSetAttribute(f, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn);
@@ -1258,12 +1261,13 @@ cudaError_t launch_process_raw(const DevSchema& S, const DevTables& T, const Lau
   chunk = (chunk + 31u) & ~31u;
   const bool big = big_override < 0 ? S.big_messages != 0 : big_override != 0;
   // the reference's own schema (small messages, integer values): the kernel with the schema folded in
-  const bool prog = intv && !big && !G.generic_only && progress_schema_matches(S);
-  if (prog) k_process_raw<true, false, true><<<grid, kRawThreads, smem, st>>>(S, T, payload, offsets, ts, n, chunk, ns);
-  else if (intv && !big) k_process_raw<true, false, false><<<grid, kRawThreads, smem, st>>>(S, T, payload, offsets, ts, n, chunk, ns);
-  else if (intv) k_process_raw<true, true, false><<<grid, kRawThreads, smem, st>>>(S, T, payload, offsets, ts, n, chunk, ns);
-  else if (!big) k_process_raw<false, false, false><<<grid, kRawThreadsF64, smem, st>>>(S, T, payload, offsets, ts, n, chunk, ns);
-  else k_process_raw<false, true, false><<<grid, kRawThreadsF64, smem, st>>>(S, T, payload, offsets, ts, n, chunk, ns);
+  const int prog = intv && !big && !G.generic_only ? progress_schema_variant(S) : 0;
+  if (prog == 1) k_process_raw<true, false, 1><<<grid, kRawThreads, smem, st>>>(S, T, payload, offsets, ts, n, chunk, ns);
+  else if (prog == 2) k_process_raw<true, false, 2><<<grid, kRawThreads, smem, st>>>(S, T, payload, offsets, ts, n, chunk, ns);
+  else if (intv && !big) k_process_raw<true, false, 0><<<grid, kRawThreads, smem, st>>>(S, T, payload, offsets, ts, n, chunk, ns);
+  else if (intv) k_process_raw<true, true, 0><<<grid, kRawThreads, smem, st>>>(S, T, payload, offsets, ts, n, chunk, ns);
+  else if (!big) k_process_raw<false, false, 0><<<grid, kRawThreadsF64, smem, st>>>(S, T, payload, offsets, ts, n, chunk, ns);
+  else k_process_raw<false, true, 0><<<grid, kRawThreadsF64, smem, st>>>(S, T, payload, offsets, ts, n, chunk, ns);
   if (launches) (*launches)++;
   return cudaGetLastError();
 }

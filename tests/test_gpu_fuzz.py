@@ -122,3 +122,19 @@ def test_fused_kernels_aggregate_mutated_stream_like_the_oracle(generic, f64):
     assert_records_equal(got, a.snapshot(), ALL_OPS)
     d = a.dropped()
     assert (k["dropped_decode"], k["dropped_enum"], k["dropped_nan"]) == (d["decode"], d["enum"], d["nan"])
+
+
+@pytest.mark.parametrize("generic", [False, True])
+def test_reference_mode_counts_on_mutated_stream(generic):
+    n = 60_000
+    slab, off, ts = _fuzz_stream(False, 64, n, SEED + 5)
+    schema = bh.telemetry_progress()
+    with bh.Aggregator(schema, mode=L.MODE_REFERENCE, generic_kernels=generic) as g:
+        g.push_batch(slab, off)
+        g.flush()
+        counts = g.status_counts()
+        k = g.counters()
+    ref = O.Handler(schema)
+    ref.handle_slab(slab, off)
+    assert counts == ref.counts()
+    assert {"decode": k["dropped_decode"], "enum": k["dropped_enum"]} == ref.dropped()

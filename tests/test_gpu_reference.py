@@ -50,13 +50,14 @@ def test_kat_vectors_as_one_batch(group):
     assert counts == ref.counts() and dropped == ref.dropped()
 
 
+@pytest.mark.parametrize("generic", [False, True])     # the kernel with the reference's schema compiled in / the generic one
 @pytest.mark.parametrize("tag", ["c1", "small", "f64_zipf"])
-def test_golden_streams(tag):
+def test_golden_streams(tag, generic):
     e = EXPECT[tag]
     spec = SynthSpec(**e["spec"])
     slab, off, ts = generate_host(spec, 0, e["n"])
     schema = bh.telemetry_progress(L.K_DOUBLE if spec.value_f64 else L.K_INT32)
-    counts, dropped, k = _gpu_counts(schema, slab, off)
+    counts, dropped, k = _gpu_counts(schema, slab, off, generic_kernels=generic)
     assert counts == e["handler_counts"]
     assert dropped == e["handler_dropped"]
     assert k["events_ok"] + k["dropped_decode"] + k["dropped_enum"] == e["n"]
