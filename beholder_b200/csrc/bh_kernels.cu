@@ -1249,7 +1249,9 @@ cudaError_t launch_process_raw(const DevSchema& S, const DevTables& T, const Lau
                                const uint8_t* payload, const uint32_t* offsets, const uint64_t* ts,
                                uint32_t n, cudaStream_t st, int* launches, int big_override) {
   if (n == 0) return cudaSuccess;
-  const bool hist = (S.ops & BH_OP_HIST) != 0, intv = S.int_values != 0;
+  // reference mode only counts: whatever the declared type of `progress`, the (1 024-thread) integer-table
+  // kernel does it; the value the decoder hands over is never used
+  const bool hist = (S.ops & BH_OP_HIST) != 0, intv = S.int_values != 0 || S.mode == BH_MODE_REFERENCE;
   const uint32_t threads = intv ? kRawThreads : kRawThreadsF64;
   size_t wbytes = (size_t)(threads / 32) * kWarpBufAlloc + kWarpBufSlack;
   uint32_t ns = pick_smem_slots(intv, hist, G, wbytes);
