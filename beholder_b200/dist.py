@@ -86,3 +86,44 @@ class WindowExchange:
         c = self.counts.cpu().numpy()
         if (c > self.owner_stride).any():
             raise RuntimeError(f"owner_stride {self.owner_stride} too small: rows per owner {c.tolist()}")
+
+
+class PeerWindowExchange(WindowExchange):
+    """Window close over peer memory instead of NCCL: every rank's receive buffer is a torch
+    symmetric-memory tensor (mapped into all ranks of the node, NVLink / NVSwitch), and the export kernel
+    of rank r stores owner o's rows straight into block r of GPU o's buffer (`bh_export_window_peers`):
+    the compaction and the exchange are one kernel, there is no send staging buffer and no all-to-all.
+    Two stream-ordered cross-GPU barriers per close frame the stores: one after them (owners may merge),
+    one after the owner has merged and re-zeroed its buffer (peers may store again).  Same results as
+    WindowExchange; histograms are not supported (use WindowExchange).  Needs all ranks on one node."""
+
+    def __init__(self, local, owned, world: int, rank: int, owner_stride: int, device: int = 0, group=None):
+        import torch
+        import torch.distributed as dist
+        import torch.distributed._symmetric_memory as symm
+        self.local, self.owned, self.world, self.rank = local, owned, world, rank
+        self.owner_stride = owner_stride
+        dev = torch.device("cuda", device)
+        group = group or dist.group.WORLD
+        self.recv = symm.empty((world, owner_stride, RECORD_WORDS), dtype=torch.int64, device=dev)
+        self.recv.zero_()
+        self.hdl = symm.rendezvous(self.recv, group)
+        self.peer_bases = torch.tensor([int(p) for p in self.hdl.buffer_ptrs], dtype=torch.int64, device=dev)
+        self.counts = torch.zeros(world, dtype=torch.int64, device=dev)
+        self.kernel_launches_per_close = 3 + 1   # export (count, prefix, scatter-to-peers) + merge
+        torch.cuda.synchronize(dev)
+        self.hdl.barrier(channel=0)              # every buffer is zero before anyone stores
+
+    def close_all_windows(self, reset_local: bool = True):
+        import torch
+        from ._lib import BH_ALL_WINDOWS
+        st = torch.cuda.current_stream().cuda_stream
+        self.local.export_window_peers(BH_ALL_WINDOWS, self.world, self.peer_bases, self.rank, self.owner_stride,
+                                       self.counts, stream=st)
+        self.hdl.barrier(channel=0)              # all rows have arrived
+        self.owned.merge_records_device(self.recv, None, self.world * self.owner_stride, stream=st)
+        self.recv.zero_()
+        if reset_local:
+            self.local.reset_device(stream=st)
+        self.hdl.barrier(channel=1)              # nobody stores into a buffer that is still being merged / cleared
+        return self.recv

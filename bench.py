@@ -7,7 +7,7 @@
 Workload (BASELINE.json configs[1], "C2"): per GPU 100 M synthetic api.TelemetryProgress events of
 64 B, 1 000 distinct (mediaId, status) keys, 10 s tumbling windows, count/sum/min/max.  A step is one
 pass of the fused decode+aggregate kernel over those events (8 slabs of 12.5 M events = 8 launches),
-plus, at N > 1, the window-close exchange (export by owner -> NCCL all-to-all -> merge).
+plus, at N > 1, the window-close exchange (export by owner straight into the owners' buffers over NVLink, or -> NCCL all-to-all; -> merge).
 
 `value`  : events/s, inputs resident in HBM, CUDA-event timed, max over ranks.
 `e2e`    : events/s through the C-ABI ingest (bh_push_batch_pinned -> bh_flush -> bh_snapshot): pinned
@@ -232,7 +232,8 @@ def workload_config(n_gpus: int):
             "events_per_gpu": EVENTS_PER_GPU, "slabs_per_step": SLABS, "payload_bytes": PAYLOAD_BYTES, "keys": N_KEYS,
             "window_ms": WINDOW_MS, "ops": "count,sum,min,max", "key_distribution": "uniform",
             "l2_policy": "inputs (7.6 GB per GPU per step) are larger than L2; no explicit flush",
-            "parallelism": f"events sharded over {n_gpus} GPU(s); key-hash owner merge per step (all-to-all) when N>1"}
+            "parallelism": f"events sharded over {n_gpus} GPU(s); key-hash owner merge per step when N>1 "
+                           f"(export kernel stores into the owners' buffers over NVLink, or NCCL all-to-all: see 'exchange')"}
 
 
 # ------------------------------------------------------------------------------------------
@@ -279,7 +280,24 @@ def main():
     exch = None
     if world > 1:
         owned = mk()
-        exch = WindowExchange(local, owned, world, rank, owner_stride=2 * (N_KEYS * 40) // world, device=local_rank)
+        stride = 2 * (N_KEYS * 40) // world
+        exchange = os.environ.get("BEHOLDER_EXCHANGE", "peer")
+        if exchange == "peer":
+            # export kernel stores straight into the owners' buffers over NVLink (torch symmetric memory);
+            # every rank must take the same branch, so a failure anywhere sends all of them to NCCL
+            okay = torch.ones(1, device="cuda")
+            try:
+                from beholder_b200.dist import PeerWindowExchange
+                exch = PeerWindowExchange(local, owned, world, rank, owner_stride=stride, device=local_rank)
+            except Exception as e:      # noqa: BLE001 - symmetric memory unavailable on this box
+                print(f"[bench] rank {rank}: peer exchange unavailable ({e}); using NCCL all-to-all", file=sys.stderr)
+                okay.zero_()
+            dist.all_reduce(okay, op=dist.ReduceOp.MIN)
+            if okay.item() == 0:
+                exch, exchange = None, "nccl"
+        if exch is None:
+            exchange = "nccl"
+            exch = WindowExchange(local, owned, world, rank, owner_stride=stride, device=local_rank)
 
     def step(ev_mid=None):
         for p, o, t, n, _ in slabs:
@@ -461,6 +479,7 @@ def main():
                          "algorithmic_bytes_per_event": BYTES_PER_EVENT, "events_per_launch": events // SLABS,
                          "avg_launch_ms": per_launch_s * 1e3},
             "gpu_launches": launches_per_step * args.steps,
+            "exchange": (exchange if world > 1 else None),
             "clocks": clocks,
         }
         if e2e:

@@ -178,6 +178,17 @@ int bh_decode_device(bh_ctx* ctx, const uint8_t* d_payload, const uint32_t* d_of
 int bh_export_window_device(bh_ctx* ctx, uint64_t window_id, uint32_t n_owners, bh_record* d_records,
                             uint32_t* d_hist, uint64_t cap, uint64_t owner_stride,
                             uint64_t* d_owner_counts, void* stream);
+/* Multi-GPU window close without a staging copy or an all-to-all (no counterpart in the reference, which is one
+ * process): like bh_export_window_device with owner_stride > 0, but the rows of owner o are stored straight
+ * into GPU o's receive buffer over NVLink.  d_peer_bases[o] = device-visible address of owner o's buffer
+ * (n_owners blocks of owner_stride bh_record rows; peer-mapped memory, e.g. CUDA IPC / torch symmetric
+ * memory); this rank writes block `my_rank` of every buffer.  The receive buffers must be zeroed (count 0 =
+ * padding) before any rank exports, and all ranks must have finished before an owner merges: the caller puts
+ * a cross-GPU barrier on the stream before and after (beholder_b200.dist.PeerWindowExchange).  Histograms
+ * are not moved by this entry (BH_ERR_UNSUPPORTED when the context has BH_OP_HIST). */
+int bh_export_window_peers(bh_ctx* ctx, uint64_t window_id, uint32_t n_owners, const uint64_t* d_peer_bases,
+                           uint32_t my_rank, uint64_t owner_stride, uint64_t* d_owner_counts, void* stream);
+
 /* bh_export_window_device for callers that must not allocate device memory.  It has no counterpart in
  * the reference.  Who needs it: a host that fixes its GPU memory budget at start-up and forbids the
  * driver allocator afterwards (a serving process sharing the GPU under a hard memory cap, a real-time
