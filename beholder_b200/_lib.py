@@ -128,7 +128,8 @@ class BhAmqpStats(C.Structure):
 
 
 PROTOTYPES.update({
-    "bh_export_window_peers": (C.c_int, [C.c_void_p, C.c_uint64, C.c_uint32, _u64p, C.c_uint32, C.c_uint64, _u64p, C.c_void_p]),
+    "bh_export_window_peers": (C.c_int, [C.c_void_p, C.c_uint64, C.c_uint32, _u64p, _u64p, C.c_uint32, C.c_uint64, _u64p,
+                                         C.c_void_p]),
     "bh_amqp_create": (C.c_int, [C.POINTER(C.c_void_p), C.c_char_p, C.c_uint64]),
     "bh_amqp_destroy": (None, [C.c_void_p]),
     "bh_amqp_feed": (C.c_int, [C.c_void_p, _u8p, C.c_uint64, _u8p, C.c_uint64, _u32p, C.POINTER(BhAmqpDelivery), C.c_uint32,

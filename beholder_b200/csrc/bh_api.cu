@@ -704,16 +704,17 @@ int bh_export_window_device(bh_ctx* c, uint64_t window_id, uint32_t n_owners, bh
 }
 
 int bh_export_window_peers(bh_ctx* c, uint64_t window_id, uint32_t n_owners, const uint64_t* d_peer_bases,
-                           uint32_t my_rank, uint64_t owner_stride, uint64_t* d_owner_counts, void* stream) {
+                           const uint64_t* d_peer_hist_bases, uint32_t my_rank, uint64_t owner_stride,
+                           uint64_t* d_owner_counts, void* stream) {
   if (!c || !d_peer_bases || !d_owner_counts) return fail(c, BH_ERR_INVALID, "null argument");
   if (!is_pow2(n_owners) || n_owners > 1024) return fail(c, BH_ERR_INVALID, "n_owners must be a power of two <= 1024");
   if (my_rank >= n_owners || owner_stride == 0) return fail(c, BH_ERR_INVALID, "my_rank must be below n_owners and owner_stride positive");
-  if (c->S.ops & BH_OP_HIST) return fail(c, BH_ERR_UNSUPPORTED, "bh_export_window_peers does not move histograms; use bh_export_window_device");
+  if ((c->S.ops & BH_OP_HIST) && !d_peer_hist_bases) return fail(c, BH_ERR_INVALID, "this context keeps histograms: d_peer_hist_bases is required");
   DeviceGuard guard(c->device);
   cudaStream_t st = stream ? (cudaStream_t)stream : c->st_compute;
   CU(c, launch_export(c->S, c->T, window_id, n_owners, nullptr, nullptr, (uint64_t)n_owners * owner_stride, owner_stride,
                       (unsigned long long*)d_owner_counts, c->d_owner_cursor, st,
-                      (const unsigned long long*)d_peer_bases, my_rank));
+                      (const unsigned long long*)d_peer_bases, (const unsigned long long*)d_peer_hist_bases, my_rank));
   return BH_OK;
 }
 

@@ -1160,7 +1160,8 @@ __global__ void k_export_prefix(uint32_t n_owners, const unsigned long long* own
 __global__ void k_export_scatter(const __grid_constant__ DevSchema S, const __grid_constant__ DevTables T, uint64_t win,
                                  uint32_t owner_shift, bh_record* out, uint32_t* hist_out, uint64_t cap,
                                  unsigned long long* cursor, uint64_t owner_stride,
-                                 const unsigned long long* peer_base, uint32_t my_rank) {
+                                 const unsigned long long* peer_base, const unsigned long long* peer_hist_base,
+                                 uint32_t my_rank) {
   uint64_t rows = (uint64_t)T.ring * T.stride, r0 = 0;
   if (win != kNoWindow) { r0 = (uint64_t)((uint32_t)win & (T.ring - 1)) * T.stride; rows = r0 + T.stride; }
   for (uint64_t row = r0 + blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; row < rows; row += (uint64_t)gridDim.x * blockDim.x) {
@@ -1178,11 +1179,14 @@ __global__ void k_export_scatter(const __grid_constant__ DevSchema S, const __gr
     rec.max = (S.ops & BH_OP_MAX) && s.max_ord ? __longlong_as_double((long long)f64_unorder(s.max_ord)) : 0.0;
     // peer_base: owner o's receive buffer lives on GPU o (mapped peer memory, NVLink): the row goes straight
     // into block `my_rank` of it -- the export IS the exchange, no staging copy and no all-to-all
-    if (peer_base) ((bh_record*)peer_base[o])[(uint64_t)my_rank * owner_stride + (pos - (unsigned long long)o * owner_stride)] = rec;
+    const uint64_t peer_row = (uint64_t)my_rank * owner_stride + (pos - (unsigned long long)o * owner_stride);
+    if (peer_base) ((bh_record*)peer_base[o])[peer_row] = rec;
     else out[pos] = rec;
-    if (hist_out && T.hist) {
+    uint32_t* hdst = peer_base ? (peer_hist_base ? (uint32_t*)peer_hist_base[o] + peer_row * T.hist_buckets : nullptr)
+                               : (hist_out ? hist_out + pos * T.hist_buckets : nullptr);
+    if (hdst && T.hist) {
       const uint32_t* h = T.hist + (base + slot) * T.hist_buckets;
-      for (uint32_t b = 0; b < T.hist_buckets; b++) hist_out[pos * T.hist_buckets + b] = h[b];
+      for (uint32_t b = 0; b < T.hist_buckets; b++) hdst[b] = h[b];
     }
   }
 }
@@ -1318,7 +1322,8 @@ static uint32_t owner_shift_of(uint32_t n_owners) {
 cudaError_t launch_export(const DevSchema& S, const DevTables& T, uint64_t window_id, uint32_t n_owners,
                           bh_record* out, uint32_t* hist_out, uint64_t cap, uint64_t owner_stride,
                           unsigned long long* owner_counts, unsigned long long* owner_cursor,
-                          cudaStream_t st, const unsigned long long* peer_base, uint32_t my_rank) {
+                          cudaStream_t st, const unsigned long long* peer_base, const unsigned long long* peer_hist_base,
+                          uint32_t my_rank) {
   cudaError_t e = cudaMemsetAsync(owner_counts, 0, sizeof(unsigned long long) * n_owners, st);
   if (e != cudaSuccess) return e;
   uint32_t shift = owner_shift_of(n_owners);
@@ -1328,7 +1333,7 @@ cudaError_t launch_export(const DevSchema& S, const DevTables& T, uint64_t windo
   k_export_count<<<(uint32_t)blocks, 256, 0, st>>>(T, window_id, shift, owner_counts);
   k_export_prefix<<<1, 32, 0, st>>>(n_owners, owner_counts, owner_cursor, owner_stride);
   k_export_scatter<<<(uint32_t)blocks, 256, 0, st>>>(S, T, window_id, shift, out, hist_out, cap, owner_cursor, owner_stride,
-                                                     peer_base, my_rank);
+                                                     peer_base, peer_hist_base, my_rank);
   return cudaGetLastError();
 }
 

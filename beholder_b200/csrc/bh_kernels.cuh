@@ -30,7 +30,8 @@ cudaError_t launch_decode(const DevSchema& S, const LaunchGeom& G, const uint8_t
 cudaError_t launch_export(const DevSchema& S, const DevTables& T, uint64_t window_id, uint32_t n_owners,
                           bh_record* out, uint32_t* hist_out, uint64_t cap, uint64_t owner_stride,
                           unsigned long long* owner_counts, unsigned long long* owner_cursor,
-                          cudaStream_t st, const unsigned long long* peer_base = nullptr, uint32_t my_rank = 0);
+                          cudaStream_t st, const unsigned long long* peer_base = nullptr,
+                          const unsigned long long* peer_hist_base = nullptr, uint32_t my_rank = 0);
 cudaError_t launch_export_static(const DevSchema& S, const DevTables& T, uint64_t window_id, uint32_t n_owners,
                                  bh_record* out, uint32_t* hist_out, uint64_t cap, uint64_t owner_stride,
                                  unsigned long long* owner_counts, cudaStream_t st);

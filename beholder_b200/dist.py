@@ -91,13 +91,14 @@ class WindowExchange:
 class PeerWindowExchange(WindowExchange):
     """Window close over peer memory instead of NCCL: every rank's receive buffer is a torch
     symmetric-memory tensor (mapped into all ranks of the node, NVLink / NVSwitch), and the export kernel
-    of rank r stores owner o's rows straight into block r of GPU o's buffer (`bh_export_window_peers`):
-    the compaction and the exchange are one kernel, there is no send staging buffer and no all-to-all.
-    Two stream-ordered cross-GPU barriers per close frame the stores: one after them (owners may merge),
-    one after the owner has merged and re-zeroed its buffer (peers may store again).  Same results as
-    WindowExchange; histograms are not supported (use WindowExchange).  Needs all ranks on one node."""
+    of rank r stores owner o's rows (and histograms, with `hist_buckets`) straight into block r of GPU o's
+    buffer (`bh_export_window_peers`): the compaction and the exchange are one kernel, there is no send
+    staging buffer and no all-to-all.  Two stream-ordered cross-GPU barriers per close frame the stores:
+    one after them (owners may merge), one after the owner has merged and re-zeroed its buffer (peers may
+    store again).  Same results as WindowExchange.  Needs all ranks on one node."""
 
-    def __init__(self, local, owned, world: int, rank: int, owner_stride: int, device: int = 0, group=None):
+    def __init__(self, local, owned, world: int, rank: int, owner_stride: int, device: int = 0, group=None,
+                 hist_buckets: int = 0):
         import torch
         import torch.distributed as dist
         import torch.distributed._symmetric_memory as symm
@@ -109,6 +110,12 @@ class PeerWindowExchange(WindowExchange):
         self.recv.zero_()
         self.hdl = symm.rendezvous(self.recv, group)
         self.peer_bases = torch.tensor([int(p) for p in self.hdl.buffer_ptrs], dtype=torch.int64, device=dev)
+        self.recv_hist = self.peer_hist_bases = None
+        if hist_buckets:
+            self.recv_hist = symm.empty((world, owner_stride, hist_buckets), dtype=torch.int32, device=dev)
+            self.recv_hist.zero_()
+            self.hdl_hist = symm.rendezvous(self.recv_hist, group)
+            self.peer_hist_bases = torch.tensor([int(p) for p in self.hdl_hist.buffer_ptrs], dtype=torch.int64, device=dev)
         self.counts = torch.zeros(world, dtype=torch.int64, device=dev)
         self.kernel_launches_per_close = 3 + 1   # export (count, prefix, scatter-to-peers) + merge
         torch.cuda.synchronize(dev)
@@ -119,10 +126,10 @@ class PeerWindowExchange(WindowExchange):
         from ._lib import BH_ALL_WINDOWS
         st = torch.cuda.current_stream().cuda_stream
         self.local.export_window_peers(BH_ALL_WINDOWS, self.world, self.peer_bases, self.rank, self.owner_stride,
-                                       self.counts, stream=st)
+                                       self.counts, d_peer_hist_bases=self.peer_hist_bases, stream=st)
         self.hdl.barrier(channel=0)              # all rows have arrived
-        self.owned.merge_records_device(self.recv, None, self.world * self.owner_stride, stream=st)
-        self.recv.zero_()
+        self.owned.merge_records_device(self.recv, self.recv_hist, self.world * self.owner_stride, stream=st)
+        self.recv.zero_()                        # (histogram rows of padding records are never read)
         if reset_local:
             self.local.reset_device(stream=st)
         self.hdl.barrier(channel=1)              # nobody stores into a buffer that is still being merged / cleared

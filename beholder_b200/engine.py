@@ -138,10 +138,10 @@ class Aggregator:
                                                owner_stride, _ptr(d_owner_counts), stream or None))
 
     def export_window_peers(self, window_id: int, n_owners: int, d_peer_bases, my_rank: int, owner_stride: int,
-                            d_owner_counts, stream: int = 0) -> None:
+                            d_owner_counts, d_peer_hist_bases=None, stream: int = 0) -> None:
         """export straight into the owners' receive buffers (peer-mapped memory): see dist.PeerWindowExchange"""
-        self._ck(L.lib.bh_export_window_peers(self._ctx, window_id, n_owners, _ptr(d_peer_bases), my_rank, owner_stride,
-                                              _ptr(d_owner_counts), stream or None))
+        self._ck(L.lib.bh_export_window_peers(self._ctx, window_id, n_owners, _ptr(d_peer_bases), _ptr(d_peer_hist_bases),
+                                              my_rank, owner_stride, _ptr(d_owner_counts), stream or None))
 
     def export_window_static(self, window_id: int, n_owners: int, d_records, d_hist, cap: int, d_owner_counts,
                              owner_stride: int = 0, stream: int = 0) -> None:

@@ -184,10 +184,12 @@ int bh_export_window_device(bh_ctx* ctx, uint64_t window_id, uint32_t n_owners, 
  * (n_owners blocks of owner_stride bh_record rows; peer-mapped memory, e.g. CUDA IPC / torch symmetric
  * memory); this rank writes block `my_rank` of every buffer.  The receive buffers must be zeroed (count 0 =
  * padding) before any rank exports, and all ranks must have finished before an owner merges: the caller puts
- * a cross-GPU barrier on the stream before and after (beholder_b200.dist.PeerWindowExchange).  Histograms
- * are not moved by this entry (BH_ERR_UNSUPPORTED when the context has BH_OP_HIST). */
+ * a cross-GPU barrier on the stream before and after (beholder_b200.dist.PeerWindowExchange).
+ * d_peer_hist_bases[o] = owner o's histogram receive buffer (same row numbering, hist_buckets u32 per
+ * row); required when the context keeps histograms, NULL otherwise. */
 int bh_export_window_peers(bh_ctx* ctx, uint64_t window_id, uint32_t n_owners, const uint64_t* d_peer_bases,
-                           uint32_t my_rank, uint64_t owner_stride, uint64_t* d_owner_counts, void* stream);
+                           const uint64_t* d_peer_hist_bases, uint32_t my_rank, uint64_t owner_stride,
+                           uint64_t* d_owner_counts, void* stream);
 
 /* bh_export_window_device for callers that must not allocate device memory.  It has no counterpart in
  * the reference.  Who needs it: a host that fixes its GPU memory budget at start-up and forbids the
