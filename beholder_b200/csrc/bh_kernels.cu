@@ -64,10 +64,10 @@ __device__ __forceinline__ void g_update(const DevTables& T, uint32_t ops, uint6
 // Two layouts, chosen by the declared type of the reduced field:
 //   INTV  (int32 / sint32 / bool `progress`, the reference schema): sum as a 64-bit integer in two
 //         32-bit words, min / max as int32 -> every update is a NATIVE 32-bit shared atomic
-//         (ATOMS.ADD / ATOMS.MIN / ATOMS.MAX), no CAS loops, no divergence.  29 B per slot.
+//         (ATOMS.ADD / ATOMS.MIN / ATOMS.MAX), no CAS loops, no divergence.  32 B per slot.
 //   F64   (double / float / uint32 values, and the columnar path): sum f64, min / max as
 //         order-preserving u64; shared memory has no native 64-bit add/max, the compiler's
-//         ATOMS.CAST.SPIN loops are used.  37 B per slot.
+//         ATOMS.CAST.SPIN loops are used.  40 B per slot.
 // =========================================================================================
 // Dynamic shared memory of the aggregating kernels and their 8 outcome counters, named at file scope so
 // that every access is a plain shared-space access (32-bit address, no generic pointer kept in registers).
@@ -78,7 +78,8 @@ struct SmemTable {
   // Only the slot count is kept; the column arrays are found from it and the shared base at
   // each use: tag u32[ns] | key u64[ns] | INTV: sum_lo u32, sum_hi i32, min i32, max i32 / F64: sum f64,
   // min_inv u64, max_ord u64 | cnt u32[ns] | gslot u32[ns] (histograms only)
-  // tag = window byte << 24 | 24 bits of the key hash that do not take part in the slot index;
+  // tag = window byte << 24 | the top 24 bits of the key hash (the slot index comes from a multiply of the
+  // folded hash, so the two are as good as independent);
   // 0xFFFFFFFF = empty slot (the window byte is always < 255).
   uint32_t ns;              // power of two
   uint32_t shift;           // 32 - log2(ns)
