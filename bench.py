@@ -411,9 +411,14 @@ def main():
             barrier()
             solo = copy_gbs(5, True) if rank == 0 else 0.0      # the other ranks wait at the barrier
             barrier()
-            conc = torch.tensor([copy_gbs(5, False), solo], dtype=torch.float64, device="cuda")
+            mine = copy_gbs(5, False)
+            conc = torch.tensor([mine, solo], dtype=torch.float64, device="cuda")
             dist.all_reduce(conc, op=dist.ReduceOp.SUM)
-            pcie_concurrent, pcie_peak = conc[0].item(), conc[1].item()
+            pcie_concurrent_sum, pcie_peak = conc[0].item(), conc[1].item()
+            # same convention as every other number here: the job is done when the LAST rank is done
+            slowest = torch.tensor([5 * src.numel() / (mine * 1e9)], dtype=torch.float64, device="cuda")   # seconds
+            dist.all_reduce(slowest, op=dist.ReduceOp.MAX)
+            pcie_concurrent = world * 5 * src.numel() / slowest.item() / 1e9
             barrier()
         else:
             pcie_peak = copy_gbs(5, True)
@@ -455,10 +460,11 @@ def main():
             e2e.update({"pcie_frac": e2e["pcie_gbs"] / pcie_peak,
                         "bound": "PCIe H2D ingest (measured pinned-copy peak of this GPU in pcie_peak_gbs_per_gpu)"})
         else:
-            e2e.update({"pcie_concurrent_peak_gbs": pcie_concurrent, "pcie_frac": e2e["pcie_gbs"] / pcie_concurrent,
+            e2e.update({"pcie_concurrent_peak_gbs": pcie_concurrent, "pcie_concurrent_sum_of_rates_gbs": pcie_concurrent_sum,
+                        "pcie_frac": e2e["pcie_gbs"] / pcie_concurrent,
                         "pcie_frac_of_n_x_solo": e2e["pcie_gbs"] / (world * pcie_peak),
-                        "bound": "PCIe H2D ingest with all N GPUs copying at once (pcie_concurrent_peak_gbs, measured; "
-                                 "pcie_peak_gbs_per_gpu is one GPU copying alone)"})
+                        "bound": "PCIe H2D ingest with all N GPUs copying at once (pcie_concurrent_peak_gbs = all bytes / time "
+                                 "until the slowest GPU is done, measured; pcie_peak_gbs_per_gpu is one GPU copying alone)"})
         ing.close()
         for pb, ob, tb, *_ in pins:
             pb.free(); ob.free(); tb.free()
