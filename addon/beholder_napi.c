@@ -10,7 +10,9 @@
  *   const ctx = native.create(configBuffer)        // bh_create; configBuffer = a packed bh_config
  *   native.push(ctx, buffer, tsMs)                 // bh_push: rmsg.message.content (index.js:129)
  *   native.flush(ctx)      -> committedSeq         // bh_flush
- *   native.poll(ctx)       -> committedSeq         // bh_poll_committed (non-blocking)
+ *   native.poll(ctx)       -> committedSeq         // bh_poll_committed (non-blocking; submits a batch past its deadline)
+ *   native.submit(ctx)                             // bh_submit: hand the partial batch to the GPU now
+ *   native.onCommit(ctx, fn)                       // bh_set_commit_callback: fn(committedSeq) on the JS thread
  *   native.snapshot(ctx, windowId, cap) -> Buffer  // bh_snapshot: packed bh_record rows
  *   native.counters(ctx)   -> Buffer               // bh_get_counters
  *   native.destroy(ctx)
@@ -85,6 +87,43 @@ static napi_value Poll(napi_env env, napi_callback_info info) {
   return seq_result(env, seq);
 }
 
+static napi_value Submit(napi_env env, napi_callback_info info) {
+  size_t argc = 1; napi_value argv[1];
+  NAPI_OK(napi_get_cb_info(env, info, &argc, argv, NULL, NULL));
+  bh_ctx* ctx = unwrap(env, argv[0]);
+  int rc = bh_submit(ctx);
+  if (rc != BH_OK) return throw_bh(env, ctx, rc);
+  return NULL;
+}
+
+/* ---- completion callback: library thread -> JS thread ----
+ * bh_set_commit_callback calls on_commit_native on the library's completion thread; a threadsafe function
+ * carries the sequence number to the JS thread, where fn(committedSeq) sends the acks (index.js:151,154).
+ * The threadsafe function is unref'ed so that it does not keep the process alive by itself. */
+static void call_js_commit(napi_env env, napi_value js_cb, void* context, void* data) {
+  (void)context;
+  uint64_t seq = (uint64_t)(uintptr_t)data;
+  if (env == NULL || js_cb == NULL) return;
+  napi_value undefined, arg;
+  if (napi_get_undefined(env, &undefined) != napi_ok) return;
+  if (napi_create_bigint_uint64(env, seq, &arg) != napi_ok) return;
+  napi_call_function(env, undefined, js_cb, 1, &arg, NULL);
+}
+static void on_commit_native(void* user, uint64_t committed_seq) {
+  napi_call_threadsafe_function((napi_threadsafe_function)user, (void*)(uintptr_t)committed_seq, napi_tsfn_nonblocking);
+}
+static napi_value OnCommit(napi_env env, napi_callback_info info) {
+  size_t argc = 2; napi_value argv[2], name; napi_threadsafe_function tsfn;
+  NAPI_OK(napi_get_cb_info(env, info, &argc, argv, NULL, NULL));
+  bh_ctx* ctx = unwrap(env, argv[0]);
+  NAPI_OK(napi_create_string_utf8(env, "beholder-gpu commit", NAPI_AUTO_LENGTH, &name));
+  NAPI_OK(napi_create_threadsafe_function(env, argv[1], NULL, name, 0, 1, NULL, NULL, NULL, call_js_commit, &tsfn));
+  NAPI_OK(napi_unref_threadsafe_function(env, tsfn));
+  int rc = bh_set_commit_callback(ctx, on_commit_native, tsfn);
+  if (rc != BH_OK) return throw_bh(env, ctx, rc);
+  return NULL;
+}
+
 static napi_value Snapshot(napi_env env, napi_callback_info info) {
   size_t argc = 3; napi_value argv[3]; bool lossless; uint64_t window = 0; uint32_t cap = 4096;
   NAPI_OK(napi_get_cb_info(env, info, &argc, argv, NULL, NULL));
@@ -115,9 +154,11 @@ static napi_value Counters(napi_env env, napi_callback_info info) {
 }
 
 /* ---- AMQP 0-9-1 delivery tap (bh_amqp_*): socket bytes in, bodies pushed as one batch, tags out ----
- * amqpCreate(consumerTag) -> external;  amqpFeed(tap, ctx, chunk: Buffer, tsMs) ->
+ * amqpCreate(consumerTag) -> external;  amqpFeed(tap, ctx, chunk: Buffer, tsMs, channelNumber) ->
  *   { consumed: Number, tags: BigUint64Array }   (bodies of the deliveries completed inside `chunk`
- * are already in the ingest ring when it returns; the caller keeps chunk.slice(consumed) for the next read) */
+ * are already in the ingest ring when it returns; the caller keeps chunk.slice(consumed) for the next read).
+ * Delivery tags are per channel: only deliveries that arrived on `channelNumber` are pushed and reported
+ * (pass -1 for every channel). */
 #define TAP_SLAB (4u << 20)
 #define TAP_CAP 65536u
 typedef struct tap_box { bh_amqp* tap; uint8_t* slab; uint32_t* offsets; bh_amqp_delivery* del; } tap_box;
@@ -141,17 +182,29 @@ static napi_value AmqpCreate(napi_env env, napi_callback_info info) {
 }
 
 static napi_value AmqpFeed(napi_env env, napi_callback_info info) {
-  size_t argc = 4; napi_value argv[4]; void* data; size_t len; int64_t ts = 0; tap_box* b;
+  size_t argc = 5; napi_value argv[5]; void* data; size_t len; int64_t ts = 0; int32_t want_channel = -1; tap_box* b;
   NAPI_OK(napi_get_cb_info(env, info, &argc, argv, NULL, NULL));
   NAPI_OK(napi_get_value_external(env, argv[0], (void**)&b));
   bh_ctx* ctx = unwrap(env, argv[1]);
   NAPI_OK(napi_get_buffer_info(env, argv[2], &data, &len));
   NAPI_OK(napi_get_value_int64(env, argv[3], &ts));
+  if (argc > 4) napi_get_value_int32(env, argv[4], &want_channel);
   uint64_t pos = 0, total = 0; size_t tcap = 1024; uint64_t* tags = (uint64_t*)malloc(tcap * 8);
   for (;;) {
     uint64_t used = 0; uint32_t n = 0;
     int rc = bh_amqp_feed(b->tap, (const uint8_t*)data + pos, len - pos, b->slab, TAP_SLAB, b->offsets, b->del, TAP_CAP, &used, &n);
     pos += used;
+    const uint32_t n_raw = n;
+    if (n && want_channel >= 0) {   /* keep the wanted channel's deliveries: compact slab, offsets and tags in place */
+      uint32_t k = 0, w = 0;
+      for (uint32_t i = 0; i < n; i++) {
+        if (b->del[i].channel != (uint16_t)want_channel) continue;
+        uint32_t nb = b->offsets[i + 1] - b->offsets[i];
+        memmove(b->slab + w, b->slab + b->offsets[i], nb);
+        b->del[k] = b->del[i]; b->offsets[k] = w; w += nb; k++;
+      }
+      b->offsets[k] = w; n = k;
+    }
     if (n) {   /* one timestamp for the batch: the arrival time of the socket read */
       uint64_t* tsv = (uint64_t*)malloc((size_t)n * 8);
       for (uint32_t i = 0; i < n; i++) tsv[i] = (uint64_t)ts;
@@ -163,7 +216,7 @@ static napi_value AmqpFeed(napi_env env, napi_callback_info info) {
       total += n;
     }
     if (rc != BH_OK) { free(tags); napi_throw_error(env, NULL, bh_amqp_last_error(b->tap)); return NULL; }
-    if (!n || !used) break;
+    if (!n_raw || !used) break;
   }
   napi_value res, cv, ab, ta; void* abdata;
   NAPI_OK(napi_create_object(env, &res));
@@ -182,6 +235,8 @@ static napi_value Init(napi_env env, napi_value exports) {
     {"push", NULL, Push, NULL, NULL, NULL, napi_default, NULL},
     {"flush", NULL, Flush, NULL, NULL, NULL, napi_default, NULL},
     {"poll", NULL, Poll, NULL, NULL, NULL, napi_default, NULL},
+    {"submit", NULL, Submit, NULL, NULL, NULL, napi_default, NULL},
+    {"onCommit", NULL, OnCommit, NULL, NULL, NULL, napi_default, NULL},
     {"snapshot", NULL, Snapshot, NULL, NULL, NULL, napi_default, NULL},
     {"counters", NULL, Counters, NULL, NULL, NULL, napi_default, NULL},
     {"amqpCreate", NULL, AmqpCreate, NULL, NULL, NULL, napi_default, NULL},

@@ -17,6 +17,7 @@ BH_MAX_ENUM = 64
 BH_HIST_MAX = 64
 BH_ALL_WINDOWS = 0xFFFFFFFFFFFFFFFF
 BH_STATIC_EXPORT_MAX_OWNERS = 1024
+BH_NO_BATCH_DEADLINE = 0xFFFFFFFF
 
 # bh_status
 BH_OK = 0
@@ -54,6 +55,7 @@ class BhConfig(C.Structure):
         ("n_enum", C.c_uint32), ("enum_numbers", C.c_int32 * BH_MAX_ENUM),
         ("table_capacity", C.c_uint64), ("hash_seed", C.c_uint64), ("slab_bytes", C.c_uint64),
         ("slab_events", C.c_uint32), ("n_slabs", C.c_uint32), ("message_bytes_hint", C.c_uint32), ("flags", C.c_uint32),
+        ("max_batch_latency_ms", C.c_uint32), ("reserved0", C.c_uint32),
     ]
 
 
@@ -78,6 +80,7 @@ class BhSynthConfig(C.Structure):
     ]
 
 
+COMMIT_CB = C.CFUNCTYPE(None, C.c_void_p, C.c_uint64)   # bh_commit_cb
 _vp, _u8p, _u32p, _u64p, _f64p, _i32p = (C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p)
 
 # every symbol include/beholder_gpu.h declares: name -> (restype, argtypes)
@@ -92,6 +95,8 @@ PROTOTYPES = {
     "bh_push_columns": (C.c_int, [C.c_void_p, _u64p, _u64p, _f64p, C.c_uint64]),
     "bh_flush": (C.c_int, [C.c_void_p, C.POINTER(C.c_uint64)]),
     "bh_poll_committed": (C.c_int, [C.c_void_p, C.POINTER(C.c_uint64)]),
+    "bh_submit": (C.c_int, [C.c_void_p]),
+    "bh_set_commit_callback": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),
     "bh_host_alloc": (C.c_int, [C.POINTER(C.c_void_p), C.c_size_t]),
     "bh_host_free": (C.c_int, [C.c_void_p]),
     "bh_snapshot": (C.c_int, [C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64)]),

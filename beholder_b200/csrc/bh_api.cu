@@ -9,7 +9,11 @@
 #endif
 
 #include <algorithm>
+#include <chrono>
+#include <condition_variable>
+#include <mutex>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "bh_kernels.cuh"
@@ -58,7 +62,20 @@ struct bh_ctx {
   unsigned long long* h_small = nullptr;          // pinned, 1024 u64
   int launches = 0;
   std::string err;
+  // One lock around every entry point: the producer thread (the Node main thread / the asyncio loop) and the
+  // library's own completion thread are the two parties.  Recursive because entry points call each other.
+  std::recursive_mutex mu;
+  std::condition_variable_any cv;
+  std::thread completer;                          // started by bh_set_commit_callback
+  bool stop = false;
+  bh_commit_cb cb = nullptr;
+  void* cb_user = nullptr;
+  uint64_t reported = 0;                          // last sequence number handed to cb
+  std::chrono::steady_clock::time_point slab_t0;  // arrival of the first message of the partial slab
+  std::chrono::microseconds max_latency{5000};
+  bool no_deadline = false;
 };
+#define BH_LOCK(c) std::lock_guard<std::recursive_mutex> lock__((c)->mu)
 
 namespace {
 
@@ -218,6 +235,78 @@ int submit_current(bh_ctx* c) {
   return slab_acquire(c, c->cur);
 }
 
+// the partial slab just received its first message: start its deadline, wake the completion thread
+void slab_first_message(bh_ctx* c) {
+  c->slab_t0 = std::chrono::steady_clock::now();
+  if (c->cb) c->cv.notify_one();
+}
+
+// index.js:151,154 acks every message, and the broker stops delivering at `prefetch` unacked ones
+// (index.js:43), so a partly filled slab must not wait for more traffic: once its oldest message is older
+// than max_batch_latency it is submitted as it is.  Never blocks: if the next ring slab is still busy the
+// submit is left to the next call.
+int submit_if_due(bh_ctx* c) {
+  Slab& s = c->slabs[c->cur];
+  if (s.n == 0 || c->no_deadline) return BH_OK;
+  if (std::chrono::steady_clock::now() - c->slab_t0 < c->max_latency) return BH_OK;
+  Slab& nx = c->slabs[(c->cur + 1) % (uint32_t)c->slabs.size()];
+  if (nx.in_flight) {
+    cudaError_t e = cudaEventQuery(nx.done);
+    if (e == cudaErrorNotReady) { cudaGetLastError(); return BH_OK; }
+  }
+  return submit_current(c);
+}
+
+int poll_slabs(bh_ctx* c) {
+  for (auto& s : c->slabs) {
+    if (!s.in_flight) continue;
+    cudaError_t e = cudaEventQuery(s.done);
+    if (e == cudaSuccess) { s.in_flight = false; if (s.seq_end > c->committed) c->committed = s.seq_end; }
+    else if (e != cudaErrorNotReady) return fail(c, BH_ERR_CUDA, "cudaEventQuery: %s", cudaGetErrorString(e));
+    else cudaGetLastError();
+  }
+  return BH_OK;
+}
+
+// The completion thread: enforces the batch deadline and reports the committed sequence number
+// through the callback, so that acks do not depend on the producer calling in again (a queue that goes quiet
+// after a few messages still gets them acked).  The callback runs on this thread with no lock held; the
+// N-API shim forwards it through napi_threadsafe_function, the Python mirror through call_soon_threadsafe.
+void completer_main(bh_ctx* c) {
+  cudaSetDevice(c->device);
+  std::unique_lock<std::recursive_mutex> lk(c->mu);
+  while (!c->stop) {
+    submit_if_due(c);
+    poll_slabs(c);
+    if (c->committed > c->reported && c->cb) {
+      const uint64_t seq = c->reported = c->committed;
+      bh_commit_cb cb = c->cb; void* user = c->cb_user;
+      lk.unlock();
+      cb(user, seq);
+      lk.lock();
+      continue;
+    }
+    bool busy = false;
+    for (auto& s : c->slabs) busy = busy || s.in_flight;
+    if (busy) c->cv.wait_for(lk, std::chrono::microseconds(50));                  // a kernel is running: poll its event
+    else if (c->slabs[c->cur].n && !c->no_deadline) c->cv.wait_until(lk, c->slab_t0 + c->max_latency);
+    else c->cv.wait_for(lk, std::chrono::milliseconds(100));                      // idle: woken by the first message
+  }
+}
+
+void stop_completer(bh_ctx* c) {
+  std::thread t;
+  {
+    BH_LOCK(c);
+    c->stop = true;
+    c->cv.notify_all();
+    t.swap(c->completer);
+  }
+  if (t.joinable()) t.join();
+  BH_LOCK(c);
+  c->stop = false;
+}
+
 struct DeviceGuard {
   int prev = -1;
   explicit DeviceGuard(int dev) { cudaGetDevice(&prev); if (prev != dev) cudaSetDevice(dev); else prev = -1; }
@@ -346,6 +435,8 @@ int bh_create(const bh_config* cfg, bh_ctx** out) {
   c->slab_bytes = cfg->slab_bytes ? cfg->slab_bytes : (64ull << 20);
   c->slab_events = cfg->slab_events ? cfg->slab_events : (1u << 20);
   if (c->slab_bytes > 0xFFFFFF00ull) { fail(c, BH_ERR_INVALID, "slab_bytes must stay below 4 GiB (u32 offsets)"); return bail(BH_ERR_INVALID); }
+  if (cfg->max_batch_latency_ms == BH_NO_BATCH_DEADLINE) c->no_deadline = true;
+  else c->max_latency = std::chrono::microseconds(1000ull * (cfg->max_batch_latency_ms ? cfg->max_batch_latency_ms : 5u));
   uint32_t n_slabs = cfg->n_slabs ? cfg->n_slabs : 3;
   c->slabs.resize(n_slabs);
   {
@@ -363,6 +454,7 @@ int bh_create(const bh_config* cfg, bh_ctx** out) {
 
 void bh_destroy(bh_ctx* c) {
   if (!c) return;
+  stop_completer(c);
   DeviceGuard guard(c->device);
   if (c->st_compute) cudaStreamSynchronize(c->st_compute);
   for (auto& s : c->slabs) slab_free(s);
@@ -395,6 +487,7 @@ int bh_host_free(void* p) { return cudaFreeHost(p) == cudaSuccess ? BH_OK : BH_E
 int bh_push(bh_ctx* c, const uint8_t* payload, uint32_t len, uint64_t ts_ms) {
   if (!c || (!payload && len)) return fail(c, BH_ERR_INVALID, "null argument");
   if ((uint64_t)len > c->slab_bytes) return fail(c, BH_ERR_TOO_LARGE, "message of %u bytes exceeds slab_bytes %llu", len, (unsigned long long)c->slab_bytes);
+  BH_LOCK(c);
   DeviceGuard guard(c->device);
   Slab* s = &c->slabs[c->cur];
   if (s->bytes + len > c->slab_bytes || s->n == c->slab_events) {
@@ -402,6 +495,7 @@ int bh_push(bh_ctx* c, const uint8_t* payload, uint32_t len, uint64_t ts_ms) {
     if (rc) return rc;
     s = &c->slabs[c->cur];
   }
+  if (s->n == 0) slab_first_message(c);
   memcpy(s->h_payload + s->bytes, payload, len);
   s->h_ts[s->n] = ts_ms;
   s->bytes += len;
@@ -413,6 +507,7 @@ int bh_push(bh_ctx* c, const uint8_t* payload, uint32_t len, uint64_t ts_ms) {
 
 int bh_push_batch(bh_ctx* c, const uint8_t* slab, const uint32_t* off, const uint64_t* ts, uint32_t n) {
   if (!c || (n && (!slab || !off))) return fail(c, BH_ERR_INVALID, "null argument");
+  BH_LOCK(c);
   DeviceGuard guard(c->device);
   uint32_t i = 0;
   while (i < n) {
@@ -435,6 +530,7 @@ int bh_push_batch(bh_ctx* c, const uint8_t* slab, const uint32_t* off, const uin
     for (uint32_t k = i; k < j; k++)
       if (off[k + 1] < off[k]) return fail(c, BH_ERR_INVALID, "offsets not monotone at %u", k);
     uint64_t nb = off[j] - off[i];
+    if (s->n == 0) slab_first_message(c);
     memcpy(s->h_payload + s->bytes, slab + off[i], nb);
     for (uint32_t k = i; k < j; k++) {
       s->h_offsets[s->n + (k - i) + 1] = (uint32_t)(s->bytes + (off[k + 1] - off[i]));
@@ -451,6 +547,7 @@ int bh_push_batch(bh_ctx* c, const uint8_t* slab, const uint32_t* off, const uin
 int bh_push_batch_pinned(bh_ctx* c, const uint8_t* slab, const uint32_t* off, const uint64_t* ts, uint32_t n) {
   if (!c || (n && (!slab || !off))) return fail(c, BH_ERR_INVALID, "null argument");
   if (c->S.has_window && !ts && n) return fail(c, BH_ERR_INVALID, "ts_ms required in windowed mode");
+  BH_LOCK(c);
   DeviceGuard guard(c->device);
   // keep arrival order: anything staged through bh_push goes first
   int rc = submit_current(c);
@@ -486,6 +583,7 @@ int bh_push_columns(bh_ctx* c, const uint64_t* kh, const uint64_t* ts, const dou
   if (!c || (n && !kh)) return fail(c, BH_ERR_INVALID, "null argument");
   if (c->S.mode != BH_MODE_WINDOWED) return fail(c, BH_ERR_INVALID, "bh_push_columns needs BH_MODE_WINDOWED");
   if (c->S.has_window && !ts && n) return fail(c, BH_ERR_INVALID, "ts_ms required in windowed mode");
+  BH_LOCK(c);
   DeviceGuard guard(c->device);
   int rc = submit_current(c);
   if (rc) return rc;
@@ -522,15 +620,32 @@ int bh_push_columns(bh_ctx* c, const uint64_t* kh, const uint64_t* ts, const dou
 
 int bh_poll_committed(bh_ctx* c, uint64_t* seq) {
   if (!c) return BH_ERR_INVALID;
+  BH_LOCK(c);
   DeviceGuard guard(c->device);
-  for (auto& s : c->slabs) {
-    if (!s.in_flight) continue;
-    cudaError_t e = cudaEventQuery(s.done);
-    if (e == cudaSuccess) { s.in_flight = false; if (s.seq_end > c->committed) c->committed = s.seq_end; }
-    else if (e != cudaErrorNotReady) return fail(c, BH_ERR_CUDA, "cudaEventQuery: %s", cudaGetErrorString(e));
-    else cudaGetLastError();
-  }
+  int rc = submit_if_due(c);
+  if (rc) return rc;
+  rc = poll_slabs(c);
+  if (rc) return rc;
   if (seq) *seq = c->committed;
+  return BH_OK;
+}
+
+int bh_submit(bh_ctx* c) {
+  if (!c) return BH_ERR_INVALID;
+  BH_LOCK(c);
+  DeviceGuard guard(c->device);
+  int rc = submit_current(c);
+  if (c->cb) c->cv.notify_one();
+  return rc;
+}
+
+int bh_set_commit_callback(bh_ctx* c, bh_commit_cb cb, void* user) {
+  if (!c) return BH_ERR_INVALID;
+  stop_completer(c);
+  BH_LOCK(c);
+  c->cb = cb; c->cb_user = user;
+  c->reported = c->committed;
+  if (cb) c->completer = std::thread(completer_main, c);
   return BH_OK;
 }
 
@@ -539,6 +654,7 @@ static int ensure_export(bh_ctx* c, uint64_t cap, bool hist);
 // host-pointer merge: the restore side of bh_snapshot_hist
 int bh_restore(bh_ctx* c, const bh_record* recs, const uint32_t* hist, uint64_t n) {
   if (!c || (n && !recs)) return fail(c, BH_ERR_INVALID, "null argument");
+  BH_LOCK(c);
   DeviceGuard guard(c->device);
   int rc = submit_current(c);
   if (rc) return rc;
@@ -559,6 +675,7 @@ int bh_restore(bh_ctx* c, const bh_record* recs, const uint32_t* hist, uint64_t 
 
 int bh_sync(bh_ctx* c) {
   if (!c) return BH_ERR_INVALID;
+  BH_LOCK(c);
   DeviceGuard guard(c->device);
   CU(c, cudaStreamSynchronize(c->st_compute));
   for (auto& s : c->slabs)
@@ -568,6 +685,7 @@ int bh_sync(bh_ctx* c) {
 
 int bh_get_counters(bh_ctx* c, bh_counters* out) {
   if (!c || !out) return BH_ERR_INVALID;
+  BH_LOCK(c);
   DeviceGuard guard(c->device);
   CU(c, cudaMemcpyAsync(c->h_small, c->T.counters, 8 * 8, cudaMemcpyDeviceToHost, c->st_compute));
   CU(c, cudaStreamSynchronize(c->st_compute));
@@ -577,6 +695,7 @@ int bh_get_counters(bh_ctx* c, bh_counters* out) {
 
 int bh_flush(bh_ctx* c, uint64_t* committed_seq) {
   if (!c) return BH_ERR_INVALID;
+  BH_LOCK(c);
   DeviceGuard guard(c->device);
   int rc = submit_current(c);
   if (rc) return rc;
@@ -608,6 +727,7 @@ static int ensure_export(bh_ctx* c, uint64_t cap, bool hist) {
 
 int bh_snapshot_hist(bh_ctx* c, uint64_t window_id, bh_record* out, uint32_t* hist_out, uint64_t cap, uint64_t* n) {
   if (!c || !n || (cap && !out)) return fail(c, BH_ERR_INVALID, "null argument");
+  BH_LOCK(c);
   DeviceGuard guard(c->device);
   int rc = submit_current(c);
   if (rc) return rc;
@@ -635,6 +755,7 @@ int bh_snapshot(bh_ctx* c, uint64_t window_id, bh_record* out, uint64_t cap, uin
 
 int bh_list_windows(bh_ctx* c, uint64_t* out, uint32_t cap, uint32_t* n) {
   if (!c || !n) return BH_ERR_INVALID;
+  BH_LOCK(c);
   DeviceGuard guard(c->device);
   int rc = submit_current(c);
   if (rc) return rc;
@@ -650,6 +771,7 @@ int bh_list_windows(bh_ctx* c, uint64_t* out, uint32_t cap, uint32_t* n) {
 
 int bh_close_window(bh_ctx* c, uint64_t window_id) {
   if (!c) return BH_ERR_INVALID;
+  BH_LOCK(c);
   DeviceGuard guard(c->device);
   int rc = submit_current(c);
   if (rc) return rc;
@@ -663,6 +785,7 @@ int bh_process_device(bh_ctx* c, const uint8_t* d_payload, const uint32_t* d_off
   if (!c || (n && (!d_payload || !d_offsets))) return fail(c, BH_ERR_INVALID, "null argument");
   if (((uintptr_t)d_payload & 15) != 0) return fail(c, BH_ERR_INVALID, "d_payload must be 16-byte aligned");
   if (c->S.has_window && !d_ts && n) return fail(c, BH_ERR_INVALID, "d_ts_ms required in windowed mode");
+  BH_LOCK(c);
   DeviceGuard guard(c->device);
   cudaStream_t st = stream ? (cudaStream_t)stream : c->st_compute;
   CU(c, launch_process_raw(c->S, c->T, c->G, d_payload, d_offsets, d_ts, n, st, &c->launches));
@@ -674,6 +797,7 @@ int bh_process_columns_device(bh_ctx* c, const uint64_t* d_kh, const uint64_t* d
   if (!c || (n && !d_kh)) return fail(c, BH_ERR_INVALID, "null argument");
   if (c->S.mode != BH_MODE_WINDOWED) return fail(c, BH_ERR_INVALID, "needs BH_MODE_WINDOWED");
   if (c->S.has_window && !d_ts && n) return fail(c, BH_ERR_INVALID, "d_ts_ms required in windowed mode");
+  BH_LOCK(c);
   DeviceGuard guard(c->device);
   cudaStream_t st = stream ? (cudaStream_t)stream : c->st_compute;
   CU(c, launch_process_columns(c->S, c->T, c->G, d_kh, d_ts, d_val, n, st, &c->launches));
@@ -684,6 +808,7 @@ int bh_decode_device(bh_ctx* c, const uint8_t* d_payload, const uint32_t* d_offs
                      uint64_t* d_kh, double* d_val, int32_t* d_status, uint8_t* d_outcome, void* stream) {
   if (!c || (n && (!d_payload || !d_offsets || !d_kh || !d_val || !d_status || !d_outcome))) return fail(c, BH_ERR_INVALID, "null argument");
   if (((uintptr_t)d_payload & 15) != 0) return fail(c, BH_ERR_INVALID, "d_payload must be 16-byte aligned");
+  BH_LOCK(c);
   DeviceGuard guard(c->device);
   cudaStream_t st = stream ? (cudaStream_t)stream : c->st_compute;
   CU(c, launch_decode(c->S, c->G, d_payload, d_offsets, n, d_kh, d_val, d_status, d_outcome, st));
@@ -696,6 +821,7 @@ int bh_export_window_device(bh_ctx* c, uint64_t window_id, uint32_t n_owners, bh
   if (!c || !d_records || !d_owner_counts) return fail(c, BH_ERR_INVALID, "null argument");
   if (!is_pow2(n_owners) || n_owners > 1024) return fail(c, BH_ERR_INVALID, "n_owners must be a power of two <= 1024");
   if (owner_stride && owner_stride * n_owners > cap) return fail(c, BH_ERR_INVALID, "owner_stride * n_owners exceeds cap");
+  BH_LOCK(c);
   DeviceGuard guard(c->device);
   cudaStream_t st = stream ? (cudaStream_t)stream : c->st_compute;
   CU(c, launch_export(c->S, c->T, window_id, n_owners, d_records, d_hist, cap, owner_stride,
@@ -710,6 +836,7 @@ int bh_export_window_peers(bh_ctx* c, uint64_t window_id, uint32_t n_owners, con
   if (!is_pow2(n_owners) || n_owners > 1024) return fail(c, BH_ERR_INVALID, "n_owners must be a power of two <= 1024");
   if (my_rank >= n_owners || owner_stride == 0) return fail(c, BH_ERR_INVALID, "my_rank must be below n_owners and owner_stride positive");
   if ((c->S.ops & BH_OP_HIST) && !d_peer_hist_bases) return fail(c, BH_ERR_INVALID, "this context keeps histograms: d_peer_hist_bases is required");
+  BH_LOCK(c);
   DeviceGuard guard(c->device);
   cudaStream_t st = stream ? (cudaStream_t)stream : c->st_compute;
   CU(c, launch_export(c->S, c->T, window_id, n_owners, nullptr, nullptr, (uint64_t)n_owners * owner_stride, owner_stride,
@@ -727,6 +854,7 @@ int bh_export_window_static(bh_ctx* c, uint64_t window_id, uint32_t n_owners, bh
                 "use bh_export_window_device", n_owners, BH_STATIC_EXPORT_MAX_OWNERS);
   if (!is_pow2(n_owners)) return fail(c, BH_ERR_INVALID, "n_owners must be a power of two");
   if (owner_stride && owner_stride * n_owners > cap) return fail(c, BH_ERR_INVALID, "owner_stride * n_owners exceeds cap");
+  BH_LOCK(c);
   DeviceGuard guard(c->device);
   cudaStream_t st = stream ? (cudaStream_t)stream : c->st_compute;
   CU(c, launch_export_static(c->S, c->T, window_id, n_owners, d_records, d_hist, cap, owner_stride,
@@ -736,6 +864,7 @@ int bh_export_window_static(bh_ctx* c, uint64_t window_id, uint32_t n_owners, bh
 
 int bh_reset_device(bh_ctx* c, void* stream) {
   if (!c) return BH_ERR_INVALID;
+  BH_LOCK(c);
   DeviceGuard guard(c->device);
   cudaStream_t st = stream ? (cudaStream_t)stream : c->st_compute;
   CU(c, launch_init_tables(c->T, st));
@@ -744,6 +873,7 @@ int bh_reset_device(bh_ctx* c, void* stream) {
 
 int bh_merge_records_device(bh_ctx* c, const bh_record* d_records, const uint32_t* d_hist, uint64_t n, void* stream) {
   if (!c || (n && !d_records)) return fail(c, BH_ERR_INVALID, "null argument");
+  BH_LOCK(c);
   DeviceGuard guard(c->device);
   cudaStream_t st = stream ? (cudaStream_t)stream : c->st_compute;
   CU(c, launch_merge(c->S, c->T, d_records, d_hist, n, st));

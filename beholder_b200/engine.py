@@ -42,7 +42,8 @@ class Aggregator:
                  window_ms: int = 10_000, window_ring: int = 0, table_capacity: int = 0,
                  hist_buckets: int = 64, hist_e0: int = DEFAULT_HIST_E0, hash_seed: int = 0xBE401DE5,
                  device: int = 0, slab_bytes: int = 0, slab_events: int = 0, n_slabs: int = 0,
-                 enum_drop: bool = True, message_bytes_hint: int = 0, generic_kernels: bool = False):
+                 enum_drop: bool = True, message_bytes_hint: int = 0, generic_kernels: bool = False,
+                 max_batch_latency_ms: int = 0, flags: int = 0):
         schema = schema or telemetry_progress()
         if mode == L.MODE_WINDOWED:
             schema = schema.with_roles(key=key)
@@ -62,7 +63,9 @@ class Aggregator:
         cfg.slab_events = slab_events
         cfg.n_slabs = n_slabs
         cfg.message_bytes_hint = message_bytes_hint
-        cfg.flags = L.F_GENERIC_KERNELS if generic_kernels else 0
+        cfg.flags = (L.F_GENERIC_KERNELS if generic_kernels else 0) | flags
+        cfg.max_batch_latency_ms = max_batch_latency_ms
+        self._commit_cb = None
         fill_config(cfg, schema)
         if not enum_drop:
             cfg.n_enum = 0
@@ -77,8 +80,9 @@ class Aggregator:
     # ---- lifecycle ----
     def close(self) -> None:
         if self._ctx:
-            L.lib.bh_destroy(self._ctx)
+            L.lib.bh_destroy(self._ctx)       # stops the completion thread before anything is freed
             self._ctx = C.c_void_p()
+            self._commit_cb = None
 
     def __del__(self):
         try:
@@ -120,6 +124,17 @@ class Aggregator:
 
     def sync(self) -> None:
         self._ck(L.lib.bh_sync(self._ctx))
+
+    def submit(self) -> None:
+        """hand the partly filled ingest slab to the GPU now, without waiting for the result"""
+        self._ck(L.lib.bh_submit(self._ctx))
+
+    def set_commit_callback(self, fn) -> None:
+        """fn(committed_seq) is called on the library's completion thread whenever more events have been
+        aggregated (bh_set_commit_callback); None stops the thread"""
+        cb = L.COMMIT_CB(lambda _user, seq: fn(seq)) if fn is not None else None
+        self._ck(L.lib.bh_set_commit_callback(self._ctx, C.cast(cb, C.c_void_p) if cb is not None else None, None))
+        self._commit_cb = cb                  # keep the trampoline alive as long as the library may call it
 
     # ---- device-resident entry points (pointers or torch tensors) ----
     def process_device(self, d_payload, d_offsets, d_ts, n: int, stream: int = 0) -> None:

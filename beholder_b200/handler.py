@@ -17,6 +17,14 @@ JS wrapper a maintainer would ship.  The drop-in is:
 `handler` returns an `async rmsg => ...` callable: it copies `rmsg.message.content` into the
 pinned ingest ring (bh_push), keeps `rmsg` and acks it exactly once when the batch holding it
 has been aggregated on the GPU (index.js:151,154: every message is acked, dropped or not).
+
+Ack liveness.  The broker stops delivering once `prefetch` messages are unacknowledged (index.js:43,
+`new AMQP(addr, 100, ...)`), so acks must never wait for more traffic.  Three things guarantee that:
+the handler submits the partial batch as soon as half a prefetch window is waiting (bh_submit); the
+library submits a partial batch whose oldest message is `max_batch_latency_ms` old; and the
+library's completion thread reports finished batches through a callback, which is posted to the
+event loop (`call_soon_threadsafe`, the counterpart of napi_threadsafe_function) and sends the acks.
+Worst-case ack latency = max_batch_latency_ms + one kernel launch (tens of microseconds).
 """
 from __future__ import annotations
 
@@ -81,25 +89,48 @@ class BeholderGPU:
     """`require('beholder-gpu')(cfg)` of SURVEY §8b."""
 
     def __init__(self, schema: Optional[Schema] = None, device: int = 0, commit_every: int = 65536,
-                 slab_bytes: int = 0, slab_events: int = 0, logger=None):
+                 slab_bytes: int = 0, slab_events: int = 0, logger=None, prefetch: int = 100,
+                 max_batch_latency_ms: int = 5):
         self.schema = schema or telemetry_progress()
         self.agg = Aggregator(self.schema, mode=L.MODE_REFERENCE, device=device,
-                              slab_bytes=slab_bytes, slab_events=slab_events)
+                              slab_bytes=slab_bytes, slab_events=slab_events,
+                              max_batch_latency_ms=max_batch_latency_ms)
         self.commit_every = commit_every
         self.logger = logger
-        self._pending: Deque[Tuple[int, object]] = collections.deque()   # (sequence number, rmsg)
-        self._seq = 0
+        self._init_ack_state(prefetch)
         self.progress_updates_total = GpuCounter(self)
         self.status_agg = None
         self.trello_comments_total = HostCounter("beholder_trello_comments",
                                                  "Total trello comments crreated in this processes lifetime")
 
+    def _init_ack_state(self, prefetch: int):
+        self._pending: Deque[Tuple[int, object]] = collections.deque()   # (sequence number, rmsg)
+        self._seq = 0
+        self._unsubmitted = 0
+        # hand a batch to the GPU once half of the broker's prefetch window (index.js:43) waits for its ack
+        self.submit_at = max(1, min(self.commit_every, prefetch // 2 if prefetch else self.commit_every))
+        self._loop = None
+
+    def _attach_loop(self):
+        """first delivery: route the library's completion callback onto this event loop"""
+        self._loop = loop = asyncio.get_running_loop()
+
+        def on_commit(seq):                            # runs on the library's completion thread
+            try:
+                loop.call_soon_threadsafe(self._ack_upto, seq)
+            except RuntimeError:                       # loop already closed: commit() / close() will ack
+                pass
+        self.agg.set_commit_callback(on_commit)
+
     # -- the handler: amqp.listen('v1.telemetry.progress', gpu.handler(fn)) --
     def handler(self, side_effects: Optional[Callable[[object], Optional[Awaitable]]] = None):
         async def on_progress(rmsg):
+            if self._loop is None:
+                self._attach_loop()
             content = rmsg.message.content
             self.agg.push(bytes(content))
             self._seq += 1
+            self._unsubmitted += 1
             self._pending.append((self._seq, rmsg))
             if side_effects is not None:
                 # index.js:140-148 stay on the host, per event; their failure neither un-counts the
@@ -113,8 +144,11 @@ class BeholderGPU:
                         self.logger.warning("failed to update media progress %s", err)
             if len(self._pending) >= self.commit_every:
                 self.commit()
-            else:
-                self._ack_upto(self.agg.poll_committed())
+                return
+            if self._unsubmitted >= self.submit_at:
+                self._unsubmitted = 0
+                self.agg.submit()
+            self._ack_upto(self.agg.poll_committed())
         return on_progress
 
     # -- v1.telemetry.status (index.js:62-125): per-status counting of the sibling stream.
@@ -160,6 +194,7 @@ class BeholderGPU:
 
     def commit(self) -> int:
         """aggregate everything received so far, then ack it; returns the number of acks sent"""
+        self._unsubmitted = 0
         return self._ack_upto(self.agg.flush())
 
     def status_counts(self) -> Dict[str, int]:
@@ -175,6 +210,8 @@ class BeholderGPU:
         return self.progress_updates_total.metrics() + self.trello_comments_total.metrics()
 
     def close(self):
+        if self._loop is not None:
+            self.agg.set_commit_callback(None)         # no more calls into a loop that may be gone
         self.commit()
         self.agg.close()
         if self.status_agg is not None:
@@ -202,11 +239,15 @@ class StubRmsg:
 
     def ack(self):
         self.acks += 1
-        self._queue.acked += 1
+        self._queue._on_ack(self)
 
 
 class StubAMQP:
-    """in-memory `new AMQP(addr, prefetch, ...)` with listen()/publish() (index.js:43,62,127)"""
+    """in-memory `new AMQP(addr, prefetch, ...)` with listen()/publish() (index.js:43,62,127).
+
+    `prefetch` is AMQP's basic.qos prefetch count: the number of UNACKNOWLEDGED deliveries the broker
+    allows; a delivery slot is freed by `ack()`, not by the handler returning.  (In the reference the two
+    coincide, because its handler acks before it returns; a handler that defers acks must not rely on it.)"""
 
     def __init__(self, prefetch: int = 100):
         self.prefetch = prefetch
@@ -214,6 +255,13 @@ class StubAMQP:
         self.queues: Dict[str, List[bytes]] = collections.defaultdict(list)
         self.delivered: List[StubRmsg] = []
         self.acked = 0
+        self.max_unacked = 0
+        self._sem: Optional[asyncio.Semaphore] = None
+
+    def _on_ack(self, rmsg: "StubRmsg"):
+        self.acked += 1
+        if rmsg.acks == 1 and self._sem is not None:
+            self._sem.release()
 
     async def connect(self):
         return None
@@ -224,26 +272,28 @@ class StubAMQP:
     def publish(self, topic: str, content: bytes):
         self.queues[topic].append(content)
 
-    async def run(self):
-        """deliver everything queued, at most `prefetch` handler invocations in flight"""
-        sem = asyncio.Semaphore(self.prefetch)
-
-        async def deliver(fn, rmsg):
-            try:
-                await fn(rmsg)
-            finally:
-                sem.release()
-
+    async def run(self, drain_timeout: Optional[float] = None):
+        """deliver everything queued, never more than `prefetch` deliveries unacknowledged; with
+        `drain_timeout` also wait (at most that many seconds) until every delivery has been acked, the way a
+        consumer keeps running after the queue went quiet"""
+        self._sem = sem = asyncio.Semaphore(self.prefetch)
         tasks = []
         for topic, msgs in self.queues.items():
             fn = self.listeners.get(topic)
             if fn is None:
                 continue
             for content in msgs:
-                await sem.acquire()
+                await sem.acquire()                     # blocks here while `prefetch` deliveries are unacked
                 rmsg = StubRmsg(content, self)
                 self.delivered.append(rmsg)
-                tasks.append(asyncio.ensure_future(deliver(fn, rmsg)))
+                self.max_unacked = max(self.max_unacked, len(self.delivered) - self.acked)
+                tasks.append(asyncio.ensure_future(fn(rmsg)))
             msgs.clear()
         if tasks:
             await asyncio.gather(*tasks)
+        if drain_timeout is not None:
+            loop = asyncio.get_running_loop()
+            t_end = loop.time() + drain_timeout
+            while self.acked < len(self.delivered) and loop.time() < t_end:
+                await asyncio.sleep(0.001)
+        self._sem = None

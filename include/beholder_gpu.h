@@ -83,7 +83,13 @@ typedef struct bh_config {
   uint32_t message_bytes_hint; /* typical serialized message size; above 72 selects the kernels that stage
                                 * larger messages (results do not depend on it); 0 = small messages */
   uint32_t flags;              /* BH_F_* bits */
+  uint32_t max_batch_latency_ms; /* a partly filled ingest slab is submitted once its oldest message is this old
+                                * (checked by bh_poll_committed and by the completion thread); 0 -> 5 ms,
+                                * BH_NO_BATCH_DEADLINE -> only when full / bh_submit / bh_flush.  Bounds the ack
+                                * latency of index.js:151,154 under the prefetch limit of index.js:43. */
+  uint32_t reserved0;
 } bh_config;
+#define BH_NO_BATCH_DEADLINE 0xFFFFFFFFu
 
 /* bh_config.flags */
 enum {
@@ -135,8 +141,19 @@ int bh_push_batch_pinned(bh_ctx* ctx, const uint8_t* slab, const uint32_t* offse
 int bh_push_columns(bh_ctx* ctx, const uint64_t* key_hash, const uint64_t* ts_ms, const double* value, uint64_t n);
 /* submit the partial slab and wait until everything pushed so far is aggregated */
 int bh_flush(bh_ctx* ctx, uint64_t* committed_seq);
-/* non-blocking: number of events whose aggregation has completed on the device */
+/* non-blocking: number of events whose aggregation has completed on the device.  Also submits the partly
+ * filled slab when its oldest message has waited max_batch_latency_ms. */
 int bh_poll_committed(bh_ctx* ctx, uint64_t* seq);
+/* submit the partly filled slab now, without waiting for its aggregation (it may wait for a free ring slab).
+ * The handler calls it when half the broker's prefetch window (index.js:43) is waiting for an ack. */
+int bh_submit(bh_ctx* ctx);
+/* Completion thread: `cb(user, committed_seq)` is called from a thread the library owns whenever the
+ * committed sequence number advances; the same thread enforces max_batch_latency_ms, so messages are acked
+ * (index.js:151,154) even when the producer never calls in again.  cb runs with no library lock held and may call
+ * any bh_* function except bh_destroy and bh_set_commit_callback.  cb = NULL stops the thread.  The N-API shim
+ * forwards cb through napi_threadsafe_function so that rmsg.ack() runs on the JS thread. */
+typedef void (*bh_commit_cb)(void* user, uint64_t committed_seq);
+int bh_set_commit_callback(bh_ctx* ctx, bh_commit_cb cb, void* user);
 int bh_host_alloc(void** out, size_t bytes);   /* pinned host memory for bh_push_batch_pinned */
 int bh_host_free(void* p);
 

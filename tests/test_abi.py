@@ -41,6 +41,23 @@ def test_struct_sizes_match_the_header():
     assert sizes == [C.sizeof(L.BhConfig), C.sizeof(L.BhRecord), C.sizeof(L.BhCounters), C.sizeof(L.BhSynthConfig), C.sizeof(L.BhField)]
 
 
+def test_js_wrapper_config_offsets_match_the_header():
+    """addon/beholder-gpu.js packs a bh_config by hand: its OFF table against offsetof() of the C struct"""
+    import tempfile
+    js = open(os.path.join(ROOT, "addon", "beholder-gpu.js")).read()
+    table = re.search(r"const OFF = \{([^}]*)\}", js).group(1)
+    off = {k: int(v) for k, v in re.findall(r"(\w+):\s*(\d+)", table)}
+    names = [k for k in off if k not in ("SIZE", "FIELD_SIZE")]
+    prints = "".join(f'printf("{n} %zu\\n", offsetof(bh_config, {n}));' for n in names)
+    code = ('#include "beholder_gpu.h"\n#include <stdio.h>\n#include <stddef.h>\nint main(){' + prints +
+            'printf("SIZE %zu\\nFIELD_SIZE %zu\\n", sizeof(bh_config), sizeof(bh_field));return 0;}')
+    with tempfile.TemporaryDirectory() as d:
+        open(os.path.join(d, "t.c"), "w").write(code)
+        subprocess.check_call(["gcc", "-std=c11", "-I", os.path.join(ROOT, "include"), "-o", os.path.join(d, "t"), os.path.join(d, "t.c")])
+        want = {k: int(v) for k, v in (line.split() for line in subprocess.check_output([os.path.join(d, "t")], text=True).splitlines())}
+    assert off == want
+
+
 @pytest.mark.skipif(HAS_GPU, reason="a GPU is visible")
 def test_no_device_is_a_loud_error_not_a_fallback():
     assert L.lib.bh_device_count() == 0

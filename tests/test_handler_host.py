@@ -2,23 +2,44 @@
 deferred acks at commit, side-effect failures — with a fake aggregator standing in for the
 C-ABI context (test double only; the product has no such path)."""
 import asyncio
+import threading
 
 import beholder_b200 as bh
 from beholder_b200 import handler as H
 
 
 class FakeAgg:
-    def __init__(self):
-        self.pushed, self.committed = [], 0
+    """models the C-ABI context's ack contract: push / submit / poll_committed / flush and the completion
+    callback, which fires `latency_s` after the first message of a batch (the library's deadline)"""
+
+    def __init__(self, latency_s=None):
+        self.pushed, self.committed, self.submitted = [], 0, 0
+        self.latency_s, self.cb, self.timer, self.submits = latency_s, None, None, 0
 
     def push(self, payload, ts_ms=0):
         self.pushed.append(payload)
+        if self.latency_s is not None and self.cb is not None and self.timer is None:
+            self.timer = threading.Timer(self.latency_s, self._deadline)
+            self.timer.start()
+
+    def _deadline(self):                     # on a foreign thread, like the library's completion thread
+        self.timer = None
+        self.committed = self.submitted = len(self.pushed)
+        self.cb(self.committed)
+
+    def submit(self):
+        self.submits += 1
+        self.submitted = len(self.pushed)
+
+    def set_commit_callback(self, fn):
+        self.cb = fn
 
     def flush(self):
         self.committed = len(self.pushed)
         return self.committed
 
     def poll_committed(self):
+        self.committed = max(self.committed, self.submitted)      # a submitted batch finishes "at once"
         return self.committed
 
     def status_counts(self):
@@ -31,11 +52,10 @@ class FakeAgg:
         pass
 
 
-def _gpu(commit_every):
+def _gpu(commit_every, prefetch=0, latency_s=None):
     g = H.BeholderGPU.__new__(H.BeholderGPU)
-    g.schema = bh.telemetry_progress(); g.agg = FakeAgg(); g.commit_every = commit_every; g.logger = None
-    import collections
-    g._pending = collections.deque(); g._seq = 0
+    g.schema = bh.telemetry_progress(); g.agg = FakeAgg(latency_s); g.commit_every = commit_every; g.logger = None
+    g._init_ack_state(prefetch)
     g.progress_updates_total = H.GpuCounter(g)
     g.trello_comments_total = H.HostCounter("beholder_trello_comments")
     return g
@@ -82,3 +102,50 @@ def test_counter_shape_matches_prom_client():
         assert False
     except TypeError:
         pass
+
+
+def test_prefetch_window_never_stalls_with_default_commit_every():
+    # index.js:43: the broker holds back once 100 deliveries are unacked; commit_every (65536) is never reached
+    amqp = bh.StubAMQP(prefetch=100)
+    g = _gpu(commit_every=65536, prefetch=100)
+    amqp.listen("v1.telemetry.progress", g.handler())
+    for i in range(10_000):
+        amqp.publish("v1.telemetry.progress", b"m%d" % i)
+    asyncio.run(asyncio.wait_for(amqp.run(), timeout=20))
+    g.commit()
+    assert amqp.acked == 10_000 and all(m.acks == 1 for m in amqp.delivered)
+    assert amqp.max_unacked <= 100
+    assert g.agg.submits >= 10_000 // 50 - 1          # one submit per half prefetch window
+
+
+def test_a_few_messages_then_idle_are_acked_by_the_completion_callback():
+    amqp = bh.StubAMQP(prefetch=100)
+    g = _gpu(commit_every=65536, prefetch=100, latency_s=0.005)
+    amqp.listen("v1.telemetry.progress", g.handler())
+    for i in range(10):
+        amqp.publish("v1.telemetry.progress", b"m%d" % i)
+    asyncio.run(amqp.run(drain_timeout=5.0))           # nobody calls commit(): the deadline must do it
+    assert amqp.acked == 10 and all(m.acks == 1 for m in amqp.delivered)
+    assert g.agg.submits == 0
+
+
+def test_stub_prefetch_counts_unacked_deliveries_not_running_handlers():
+    # a handler that returns without acking must block the queue at `prefetch`
+    amqp = bh.StubAMQP(prefetch=3)
+    got = []
+
+    async def lazy(rmsg):
+        got.append(rmsg)
+    amqp.listen("q", lazy)
+    for i in range(5):
+        amqp.publish("q", b"x")
+
+    async def scenario():
+        t = asyncio.ensure_future(amqp.run())
+        await asyncio.sleep(0.05)
+        assert len(got) == 3 and not t.done()          # stuck behind 3 unacked deliveries
+        for m in list(got):
+            m.ack()
+        await asyncio.wait_for(t, timeout=5)
+    asyncio.run(scenario())
+    assert len(got) == 5
