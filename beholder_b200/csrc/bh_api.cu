@@ -61,6 +61,12 @@ struct bh_ctx {
   uint64_t export_cap = 0;
   unsigned long long* h_small = nullptr;          // pinned, 1024 u64
   int launches = 0;
+  // partitioned mode (DevTables::part_*): tuples logged since the last drain (upper bound), the fill at which a
+  // drain is forced before the next launch, and the stream the log was last written on
+  uint64_t part_pending = 0, part_limit = 0;
+  bool part_f64_tuples = false;                   // the log holds values that did not come from an int32 field
+  cudaStream_t part_stream = nullptr;
+  cudaEvent_t part_ev = nullptr;
   std::string err;
   // One lock around every entry point: the producer thread (the Node main thread / the asyncio loop) and the
   // library's own completion thread are the two parties.  Recursive because entry points call each other.
@@ -205,11 +211,37 @@ int slab_acquire(bh_ctx* c, uint32_t i) {
   return BH_OK;
 }
 
+// Partitioned mode.  part_drain folds the logged tuples into the tables on the stream that wrote them and makes
+// `st` wait for it; every entry point that reads, exports, closes or resets tables calls it first.
+int part_drain(bh_ctx* c, cudaStream_t st) {
+  if (!c->T.part_lg || c->part_pending == 0) return BH_OK;
+  cudaStream_t ps = c->part_stream ? c->part_stream : c->st_compute;
+  CU(c, launch_part_drain(c->S, c->T, c->G, c->S.int_values != 0 && !c->part_f64_tuples, ps, &c->launches));
+  c->part_pending = 0; c->part_f64_tuples = false;
+  if (st != ps) {
+    CU(c, cudaEventRecord(c->part_ev, ps));
+    CU(c, cudaStreamWaitEvent(st, c->part_ev, 0));
+  }
+  return BH_OK;
+}
+// before a launch that may log up to n tuples on `st`
+int part_reserve(bh_ctx* c, uint64_t n, cudaStream_t st, bool f64_values) {
+  if (!c->T.part_lg) return BH_OK;
+  if (c->part_pending && (c->part_pending + n > c->part_limit || (c->part_stream && c->part_stream != st))) {
+    int rc = part_drain(c, st);
+    if (rc) return rc;
+  }
+  c->part_pending += n; c->part_stream = st;
+  c->part_f64_tuples = c->part_f64_tuples || f64_values;
+  return BH_OK;
+}
+
 // launch the fused kernel over what slab `s` holds on the device; `virt` is the payload base the
 // offsets are relative to
 int slab_launch(bh_ctx* c, Slab& s, const uint8_t* virt, uint32_t n, bool with_ts, cudaStream_t copy_stream, uint64_t bytes) {
   CU(c, cudaEventRecord(s.copied, copy_stream));
   CU(c, cudaStreamWaitEvent(c->st_compute, s.copied, 0));
+  { int rc = part_reserve(c, n, c->st_compute, false); if (rc) return rc; }
   // the ingest path knows the slab's byte count: pick the kernel variant from the real average size
   CU(c, launch_process_raw(c->S, c->T, c->G, virt, s.d_offsets, with_ts ? s.d_ts : nullptr, n, c->st_compute, &c->launches,
                            n && bytes / n > 72 ? 1 : 0));
@@ -427,6 +459,23 @@ int bh_create(const bh_config* cfg, bh_ctx** out) {
   CUB_(cudaMalloc((void**)&T.stats, rows * sizeof(Stat)));
   if (S.ops & BH_OP_HIST) CUB_(cudaMalloc((void**)&T.hist, rows * S.hist_buckets * 4));
   CUB_(cudaMalloc((void**)&T.counters, 8 * 8));
+  // partitioned (deferred) aggregation: on request, or by itself once a window's table is too large for L2
+  const bool part = cfg->mode == BH_MODE_WINDOWED && !(cfg->flags & BH_F_NO_PARTITION) &&
+                    ((cfg->flags & BH_F_PARTITIONED) || cap >= (1ull << 18));
+  if (part) {
+    uint32_t lg = 0;
+    while ((1ull << lg) < cap) lg++;
+    lg = lg > 22 ? 12 : (lg < 16 ? 6 : lg - 10);                 // ~1024 table slots per partition, 64 .. 4096 partitions
+    while ((1u << lg) < ring) lg++;                              // a tuple carries its ring slot in the partition bits
+    T.part_lg = lg;
+    T.part_cap = cfg->part_region_tuples ? cfg->part_region_tuples : 512;
+    T.part_ctas = (uint32_t)prop.multiProcessorCount;
+    const size_t regions = (size_t)T.part_ctas << lg;
+    CUB_(cudaMalloc((void**)&T.part_tuples, regions * T.part_cap * sizeof(uint4)));
+    CUB_(cudaMalloc((void**)&T.part_fill, regions * 4));
+    CUB_(cudaEventCreateWithFlags(&c->part_ev, cudaEventDisableTiming));
+    c->part_limit = (uint64_t)((double)regions * T.part_cap * 0.6);   // mean fill 0.6: a uniform stream stays > 10 sigma below a region's end
+  }
   CUB_(cudaMalloc((void**)&c->d_owner_counts, 1024 * 8));
   CUB_(cudaMalloc((void**)&c->d_owner_cursor, 1024 * 8));
   CUB_(cudaHostAlloc((void**)&c->h_small, 1024 * 8, cudaHostAllocDefault));
@@ -463,6 +512,9 @@ void bh_destroy(bh_ctx* c) {
   if (c->T.stats) cudaFree(c->T.stats);
   if (c->T.hist) cudaFree(c->T.hist);
   if (c->T.counters) cudaFree(c->T.counters);
+  if (c->T.part_tuples) cudaFree(c->T.part_tuples);
+  if (c->T.part_fill) cudaFree(c->T.part_fill);
+  if (c->part_ev) cudaEventDestroy(c->part_ev);
   if (c->d_owner_counts) cudaFree(c->d_owner_counts);
   if (c->d_owner_cursor) cudaFree(c->d_owner_cursor);
   if (c->d_export) cudaFree(c->d_export);
@@ -606,6 +658,8 @@ int bh_push_columns(bh_ctx* c, const uint64_t* kh, const uint64_t* ts, const dou
     CU(c, cudaEventRecord(s.copied, cs));
     CU(c, cudaStreamWaitEvent(c->st_compute, s.copied, 0));
     c->pushed += m;
+    rc = part_reserve(c, m, c->st_compute, true);
+    if (rc) return rc;
     CU(c, launch_process_columns(c->S, c->T, c->G, d_kh, d_ts, val ? d_val : nullptr, m, c->st_compute, &c->launches));
     CU(c, cudaEventRecord(s.done, c->st_compute));
     s.in_flight = true; s.seq_end = c->pushed;
@@ -677,6 +731,7 @@ int bh_sync(bh_ctx* c) {
   if (!c) return BH_ERR_INVALID;
   BH_LOCK(c);
   DeviceGuard guard(c->device);
+  { int rc = part_drain(c, c->st_compute); if (rc) return rc; }
   CU(c, cudaStreamSynchronize(c->st_compute));
   for (auto& s : c->slabs)
     if (s.in_flight) { s.in_flight = false; if (s.seq_end > c->committed) c->committed = s.seq_end; }
@@ -687,6 +742,7 @@ int bh_get_counters(bh_ctx* c, bh_counters* out) {
   if (!c || !out) return BH_ERR_INVALID;
   BH_LOCK(c);
   DeviceGuard guard(c->device);
+  { int rc = part_drain(c, c->st_compute); if (rc) return rc; }
   CU(c, cudaMemcpyAsync(c->h_small, c->T.counters, 8 * 8, cudaMemcpyDeviceToHost, c->st_compute));
   CU(c, cudaStreamSynchronize(c->st_compute));
   memcpy(out, c->h_small, sizeof(bh_counters));
@@ -735,6 +791,8 @@ int bh_snapshot_hist(bh_ctx* c, uint64_t window_id, bh_record* out, uint32_t* hi
   rc = ensure_export(c, cap, hist);
   if (rc) return rc;
   uint64_t dcap = std::min<uint64_t>(cap, c->export_cap);
+  rc = part_drain(c, c->st_compute);
+  if (rc) return rc;
   CU(c, launch_export(c->S, c->T, window_id, 1, c->d_export, hist ? c->d_export_hist : nullptr, dcap, 0,
                       c->d_owner_counts, c->d_owner_cursor, c->st_compute));
   CU(c, cudaMemcpyAsync(c->h_small, c->d_owner_counts, 8, cudaMemcpyDeviceToHost, c->st_compute));
@@ -775,6 +833,8 @@ int bh_close_window(bh_ctx* c, uint64_t window_id) {
   DeviceGuard guard(c->device);
   int rc = submit_current(c);
   if (rc) return rc;
+  rc = part_drain(c, c->st_compute);
+  if (rc) return rc;
   CU(c, launch_close_window(c->T, window_id, c->st_compute));
   return BH_OK;
 }
@@ -788,6 +848,7 @@ int bh_process_device(bh_ctx* c, const uint8_t* d_payload, const uint32_t* d_off
   BH_LOCK(c);
   DeviceGuard guard(c->device);
   cudaStream_t st = stream ? (cudaStream_t)stream : c->st_compute;
+  { int rc = part_reserve(c, n, st, false); if (rc) return rc; }
   CU(c, launch_process_raw(c->S, c->T, c->G, d_payload, d_offsets, d_ts, n, st, &c->launches));
   return BH_OK;
 }
@@ -800,6 +861,7 @@ int bh_process_columns_device(bh_ctx* c, const uint64_t* d_kh, const uint64_t* d
   BH_LOCK(c);
   DeviceGuard guard(c->device);
   cudaStream_t st = stream ? (cudaStream_t)stream : c->st_compute;
+  { int rc = part_reserve(c, n, st, true); if (rc) return rc; }
   CU(c, launch_process_columns(c->S, c->T, c->G, d_kh, d_ts, d_val, n, st, &c->launches));
   return BH_OK;
 }
@@ -824,6 +886,7 @@ int bh_export_window_device(bh_ctx* c, uint64_t window_id, uint32_t n_owners, bh
   BH_LOCK(c);
   DeviceGuard guard(c->device);
   cudaStream_t st = stream ? (cudaStream_t)stream : c->st_compute;
+  { int rc = part_drain(c, st); if (rc) return rc; }
   CU(c, launch_export(c->S, c->T, window_id, n_owners, d_records, d_hist, cap, owner_stride,
                       (unsigned long long*)d_owner_counts, c->d_owner_cursor, st));
   return BH_OK;
@@ -839,6 +902,7 @@ int bh_export_window_peers(bh_ctx* c, uint64_t window_id, uint32_t n_owners, con
   BH_LOCK(c);
   DeviceGuard guard(c->device);
   cudaStream_t st = stream ? (cudaStream_t)stream : c->st_compute;
+  { int rc = part_drain(c, st); if (rc) return rc; }
   CU(c, launch_export(c->S, c->T, window_id, n_owners, nullptr, nullptr, (uint64_t)n_owners * owner_stride, owner_stride,
                       (unsigned long long*)d_owner_counts, c->d_owner_cursor, st,
                       (const unsigned long long*)d_peer_bases, (const unsigned long long*)d_peer_hist_bases, my_rank));
@@ -857,6 +921,7 @@ int bh_export_window_static(bh_ctx* c, uint64_t window_id, uint32_t n_owners, bh
   BH_LOCK(c);
   DeviceGuard guard(c->device);
   cudaStream_t st = stream ? (cudaStream_t)stream : c->st_compute;
+  { int rc = part_drain(c, st); if (rc) return rc; }
   CU(c, launch_export_static(c->S, c->T, window_id, n_owners, d_records, d_hist, cap, owner_stride,
                              (unsigned long long*)d_owner_counts, st));
   return BH_OK;
@@ -867,6 +932,11 @@ int bh_reset_device(bh_ctx* c, void* stream) {
   BH_LOCK(c);
   DeviceGuard guard(c->device);
   cudaStream_t st = stream ? (cudaStream_t)stream : c->st_compute;
+  if (c->part_pending && c->part_stream && c->part_stream != st) {   // order the reset after the kernels that still write the log
+    CU(c, cudaEventRecord(c->part_ev, c->part_stream));
+    CU(c, cudaStreamWaitEvent(st, c->part_ev, 0));
+  }
+  c->part_pending = 0; c->part_f64_tuples = false;                  // launch_init_tables empties the log as well
   CU(c, launch_init_tables(c->T, st));
   return BH_OK;
 }

@@ -17,6 +17,14 @@ namespace bh {
 // ---------------------------------------------------------------------------------------
 constexpr uint64_t kHashInit = 0x6A09E667F3BCC908ull;
 constexpr uint64_t kHashMul = 0x9E3779B97F4A7C15ull;
+// kHashMul^-1 mod 2^64 (Newton: x <- x * (2 - a x) doubles the correct low bits; a is odd, a*a = 1 mod 8)
+constexpr uint64_t inv_mod_2_64(uint64_t a) {
+  uint64_t x = a;
+  for (int i = 0; i < 6; i++) x *= 2 - a * x;
+  return x;
+}
+constexpr uint64_t kHashMulInv = inv_mod_2_64(kHashMul);
+static_assert(kHashMul * kHashMulInv == 1ull, "modular inverse");
 
 // One word into the state: xor, 64-bit multiply, then a second, 32-bit multiply of the product's low half
 // mixed with its high half rotated by 16, halves swapped.  Why two multiplies: a bit that sits at
@@ -154,6 +162,18 @@ struct DevTables {
   uint64_t stride;               // cap + 2 (side slots for the two sentinel-valued keys)
   uint32_t ring;                 // power of two
   uint32_t hist_buckets;
+  // ---- partitioned (deferred) aggregation for large key sets; part_lg == 0: off ----
+  // An event that misses the per-CTA shared-memory table is not applied to the HBM tables at once (one random
+  // DRAM line per table per event) but appended as a 16-byte tuple to the region [CTA][partition] of a log,
+  // partition = top part_lg bits of key_hash * kHashMul = the top bits of its table slot, so that a
+  // partition's slots are one contiguous slice of every window's table.  k_part_drain later gives each
+  // partition to ONE CTA, which aggregates its tuples in shared memory and touches only that slice.
+  uint4* part_tuples;            // [part_ctas][P][part_cap]: {hs low bits | ring slot << (64 - part_lg), value bits}
+  uint32_t* part_fill;           // [part_ctas][P] tuples in each region (kept between the launches of an epoch)
+  uint32_t part_lg;              // log2(P)
+  uint32_t part_cap;             // tuples per region
+  uint32_t part_ctas;            // regions per partition = the largest grid of the scattering kernels
+  uint32_t part_smem_off;        // where a scattering kernel keeps its P cursors in dynamic shared memory (set per launch)
 };
 
 enum CounterIdx { C_OK = 0, C_DECODE = 1, C_ENUM = 2, C_NAN = 3, C_TABLE_FULL = 4, C_WINDOW = 5, C_SPILL = 6, C_SLOW = 7 };

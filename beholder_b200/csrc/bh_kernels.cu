@@ -99,6 +99,7 @@ struct SmemTable {
   __device__ __forceinline__ unsigned long long* fmax_ord() const { return (unsigned long long*)(g_smem + (size_t)ns * 28); }
 };
 constexpr int kSmemProbes = 16;
+constexpr int kSmemProbesPart = 6;   // scattering kernels: a miss only costs a 16-byte append, so give up sooner
 constexpr uint32_t kTagEmpty = 0xFFFFFFFFu;
 __device__ __forceinline__ uint32_t smem_tag(uint64_t kh, uint32_t wrel) { return (wrel << 24) | (uint32_t)(kh >> 40); }
 __host__ __device__ constexpr uint32_t smem_slot_bytes(bool intv, bool hist) {
@@ -161,7 +162,7 @@ __device__ __noinline__ int smem_insert(const SmemTable M, const DevTables& T, u
 }
 
 // Hot half: read-only look-up (plain shared loads, no atomics, no waiting).
-template <bool INTV>
+template <bool INTV, bool PART_OK>
 __device__ __forceinline__ int smem_find_or_insert(const SmemTable& M, const DevTables& T, uint64_t kh,
                                                    uint32_t wrel, uint64_t win) {
   const uint32_t x = (uint32_t)kh ^ (uint32_t)(kh >> 32) ^ (wrel * 0x85EBCA6Bu);
@@ -169,7 +170,7 @@ __device__ __forceinline__ int smem_find_or_insert(const SmemTable& M, const Dev
   const uint32_t tag = smem_tag(kh, wrel), mask = M.ns - 1;
   const uint32_t* tags = M.tag();
   uint32_t t = tags[slot];
-  int left = kSmemProbes;
+  int left = PART_OK && T.part_lg ? kSmemProbesPart : kSmemProbes;
 #pragma unroll 1
   while (t != tag && t != kTagEmpty) {
     if (--left == 0) return -1;
@@ -188,16 +189,51 @@ struct LaneCounters {
   __device__ __forceinline__ void bump(uint32_t which) { atomicAdd(&g_cnt[which], 1u); }   // g_cnt: zeroed by the kernel
 };
 
+// Partitioned mode (DevTables::part_*): append the event to this CTA's region of its partition.  Returns false
+// when it has to take the direct path after all: region full (a skewed key distribution; the direct path is
+// where hot keys are cheap, they stay in L2) or the window's ring slot is held by another window.
+__device__ __noinline__ bool part_scatter(const DevTables& T, uint64_t kh, uint64_t win, uint64_t vbits) {
+  const uint32_t r = (uint32_t)win & (T.ring - 1);
+  unsigned long long w = T.ring_win[r];
+  if (w != win) {                                       // claim the ring slot now: the drain resolves r -> window id
+    if (w != kNoWindow) return false;
+    const unsigned long long old = atomicCAS(&T.ring_win[r], (unsigned long long)kNoWindow, (unsigned long long)win);
+    if (old != kNoWindow && old != win) return false;
+  }
+  const uint32_t sh = 64u - T.part_lg;
+  const uint64_t hs = kh * kHashMul;
+  const uint32_t p = (uint32_t)(hs >> sh);
+  uint32_t* cur = (uint32_t*)(g_smem + T.part_smem_off);
+  const uint32_t pos = atomicAdd(&cur[p], 1u);
+  if (pos >= T.part_cap) return false;
+  const uint64_t a = (hs & ((1ull << sh) - 1)) | ((uint64_t)r << sh);
+  T.part_tuples[((uint64_t)blockIdx.x << T.part_lg | p) * T.part_cap + pos] =
+      make_uint4((uint32_t)a, (uint32_t)(a >> 32), (uint32_t)vbits, (uint32_t)(vbits >> 32));
+  return true;
+}
+// cursors of this CTA's regions: global <-> shared at the two ends of a scattering kernel
+__device__ __forceinline__ void part_cursors_load(const DevTables& T) {
+  if (!T.part_lg) return;
+  uint32_t* cur = (uint32_t*)(g_smem + T.part_smem_off);
+  for (uint32_t i = threadIdx.x; i < (1u << T.part_lg); i += blockDim.x) cur[i] = T.part_fill[((uint64_t)blockIdx.x << T.part_lg) + i];
+}
+__device__ __forceinline__ void part_cursors_store(const DevTables& T) {
+  if (!T.part_lg) return;
+  const uint32_t* cur = (const uint32_t*)(g_smem + T.part_smem_off);
+  for (uint32_t i = threadIdx.x; i < (1u << T.part_lg); i += blockDim.x) T.part_fill[((uint64_t)blockIdx.x << T.part_lg) + i] = min(cur[i], T.part_cap);
+}
+
 // One event into the tables.  `wbase` is the CTA's first window minus one.
 // INTV: `iv` is the value; otherwise `v`.  `mask` = the lanes that call it together.
-template <bool INTV>
+// PART_OK = false (the drain kernel): a miss goes to the HBM table directly even in partitioned mode.
+template <bool INTV, bool PART_OK = true>
 __device__ __forceinline__ void aggregate_event(const DevSchema& S, const DevTables& T, const SmemTable& M,
                                                 uint64_t kh, uint64_t win, uint64_t wbase, double v, int32_t iv,
                                                 LaneCounters& C, uint32_t mask) {
   const uint32_t ops = S.ops;
   const uint64_t wr = win - wbase;
   int slot = -1;
-  if (kh < kLockKey && wr < 255ull) slot = smem_find_or_insert<INTV>(M, T, kh, (uint32_t)wr, win);
+  if (kh < kLockKey && wr < 255ull) slot = smem_find_or_insert<INTV, PART_OK>(M, T, kh, (uint32_t)wr, win);
   __syncwarp(mask);   // lanes leave the probe loop at different iterations: bring them back before the updates
   if (slot >= 0) {
     if (ops & BH_OP_HIST) {
@@ -224,6 +260,11 @@ __device__ __forceinline__ void aggregate_event(const DevSchema& S, const DevTab
       if (ops & BH_OP_MAX) atomicMax(M.fmax_ord() + slot, (unsigned long long)ord);
     }
     C.ok++;
+    return;
+  }
+  if (PART_OK && T.part_lg && kh < kLockKey &&
+      part_scatter(T, kh, win, (uint64_t)__double_as_longlong(INTV ? (double)iv : v))) {   // always the f64 bits
+    C.ok++; C.bump(C_SPILL);
     return;
   }
   // spill: straight to the HBM table
@@ -1015,6 +1056,7 @@ k_process_raw(const __grid_constant__ DevSchema S, const __grid_constant__ DevTa
   const uint32_t wb = warp_buffer_origin((uint32_t)__cvta_generic_to_shared(g_smem) +
                                          ((ns * smem_slot_bytes(INTV, hist) + 15u) & ~15u));
   smem_table_clear<INTV>(M);
+  part_cursors_load(T);
   if (threadIdx.x < 8) g_cnt[threadIdx.x] = 0;
 #ifdef BH_BOUNDS_CHECK
   if (threadIdx.x == 0) {
@@ -1036,6 +1078,7 @@ k_process_raw(const __grid_constant__ DevSchema S, const __grid_constant__ DevTa
   }
   __syncthreads();
   smem_table_flush<INTV>(S, T, M, wbase);
+  part_cursors_store(T);
   counters_flush(T, C);
 }
 
@@ -1083,6 +1126,7 @@ k_process_columns(const __grid_constant__ DevSchema S, const __grid_constant__ D
                   const double* __restrict__ val, uint64_t n, uint64_t chunk, uint32_t ns) {
   const SmemTable M = smem_table_carve<false>(ns, (S.ops & BH_OP_HIST) != 0);
   smem_table_clear<false>(M);
+  part_cursors_load(T);
   if (threadIdx.x < 8) g_cnt[threadIdx.x] = 0;
   __syncthreads();
   const uint64_t cs = min(n, (uint64_t)blockIdx.x * chunk), ce = min(n, cs + chunk);
@@ -1109,7 +1153,70 @@ k_process_columns(const __grid_constant__ DevSchema S, const __grid_constant__ D
   }
   __syncthreads();
   smem_table_flush<false>(S, T, M, wbase);
+  part_cursors_store(T);
   counters_flush(T, C);
+}
+
+// =========================================================================================
+// partitioned mode, second phase: one CTA per partition folds the logged tuples into the tables
+// =========================================================================================
+// Algorithmic bytes: 16 per logged tuple read once (coalesced, a region is contiguous), plus the partition's
+// slice of every open window's table read and written once per drain -- which is why tuples are collected over
+// many launches (an "epoch") before they are drained.  The tuples of one partition carry at most
+// keys / P distinct keys per window, so the shared table absorbs nearly all of them and the HBM slice sees one
+// update per (key, window), not one per event; what does not fit falls through to L2 atomics on a slice that
+// only this CTA is touching.  Histogram buckets go to the HBM rows directly (one L2 atomic per tuple): the
+// slice's rows stay in L2 while the partition is being drained.
+constexpr int kDrainThreads = 1024;
+__shared__ unsigned long long g_wmin;
+
+template <bool INTV>
+__global__ void __launch_bounds__(kDrainThreads, 1)
+k_part_drain(const __grid_constant__ DevSchema S, const __grid_constant__ DevTables T, uint32_t ns) {
+  const bool hist = (S.ops & BH_OP_HIST) != 0;
+  const SmemTable M = smem_table_carve<INTV>(ns, hist);
+  if (threadIdx.x == 0) g_wmin = kNoWindow;
+  if (threadIdx.x < 8) g_cnt[threadIdx.x] = 0;
+  __syncthreads();
+  for (uint32_t r = threadIdx.x; r < T.ring; r += blockDim.x) {
+    const unsigned long long w = T.ring_win[r];
+    if (w != kNoWindow) atomicMin(&g_wmin, w);
+  }
+  __syncthreads();
+  const uint64_t wbase = g_wmin == kNoWindow || g_wmin == 0 ? 0 : g_wmin - 1;
+  const uint32_t P = 1u << T.part_lg, sh = 64u - T.part_lg;
+  const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+  LaneCounters C{0u};
+  for (uint32_t p = blockIdx.x; p < P; p += gridDim.x) {
+    smem_table_clear<INTV>(M);
+    __syncthreads();
+    for (uint32_t c = warp; c < T.part_ctas; c += nwarps) {            // a warp takes whole regions
+      const uint64_t region = ((uint64_t)c << T.part_lg) | p;
+      const uint32_t n = min(T.part_fill[region], T.part_cap);
+      const uint4* src = T.part_tuples + region * T.part_cap;
+      for (uint32_t i0 = 0; i0 < n; i0 += 32) {
+        const bool valid = i0 + lane < n;
+        const uint32_t mask = __ballot_sync(0xFFFFFFFFu, valid);
+        if (!valid) continue;
+        const uint4 t = ldg_stream(src + i0 + lane);
+        const uint64_t a = ((uint64_t)t.y << 32) | t.x, vbits = ((uint64_t)t.w << 32) | t.z;
+        const uint32_t r = (uint32_t)(a >> sh);
+        const uint64_t kh = ((a & ((1ull << sh) - 1)) | ((uint64_t)p << sh)) * kHashMulInv;
+        const uint64_t win = T.ring_win[r];
+        const double v = __longlong_as_double((long long)vbits);
+        aggregate_event<INTV, false>(S, T, M, kh, win, wbase, v, INTV ? (int32_t)v : 0, C, mask);
+      }
+    }
+    __syncthreads();
+    smem_table_flush<INTV>(S, T, M, wbase);
+    for (uint32_t c = threadIdx.x; c < T.part_ctas; c += blockDim.x) T.part_fill[((uint64_t)c << T.part_lg) | p] = 0;
+    __syncthreads();
+  }
+  // the tuples were counted as aggregated when they were logged: only what was refused now moves to the drop counters
+  if (threadIdx.x == C_TABLE_FULL || threadIdx.x == C_WINDOW) {
+    const unsigned long long d = g_cnt[threadIdx.x];
+    if (d) { atomicAdd(&T.counters[threadIdx.x], d); atomicAdd(&T.counters[C_OK], 0ull - d); }
+  }
 }
 
 // =========================================================================================
@@ -1239,7 +1346,8 @@ cudaError_t configure_kernels(const LaunchGeom& G) {
   const void* fns[] = {(const void*)k_process_raw<true, false, 0>, (const void*)k_process_raw<true, true, 0>,
                        (const void*)k_process_raw<false, false, 0>, (const void*)k_process_raw<false, true, 0>,
                        (const void*)k_process_raw<true, false, 1>, (const void*)k_process_raw<true, false, 2>,
-                       (const void*)k_decode<false>, (const void*)k_decode<true>, (const void*)k_process_columns};
+                       (const void*)k_decode<false>, (const void*)k_decode<true>, (const void*)k_process_columns,
+                       (const void*)k_part_drain<true>, (const void*)k_part_drain<false>};
   for (const void* f : fns) {
     cudaError_t e = cudaFuncSetAttribute(f, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn);
     if (e != cudaSuccess) return e;
@@ -1254,7 +1362,7 @@ static uint32_t pick_smem_slots(bool intv, bool hist, const LaunchGeom& G, size_
   return ns;
 }
 
-cudaError_t launch_process_raw(const DevSchema& S, const DevTables& T, const LaunchGeom& G,
+cudaError_t launch_process_raw(const DevSchema& S, const DevTables& T0, const LaunchGeom& G,
                                const uint8_t* payload, const uint32_t* offsets, const uint64_t* ts,
                                uint32_t n, cudaStream_t st, int* launches, int big_override) {
   if (n == 0) return cudaSuccess;
@@ -1263,8 +1371,12 @@ cudaError_t launch_process_raw(const DevSchema& S, const DevTables& T, const Lau
   const bool hist = (S.ops & BH_OP_HIST) != 0, intv = S.int_values != 0 || S.mode == BH_MODE_REFERENCE;
   const uint32_t threads = intv ? kRawThreads : kRawThreadsF64;
   size_t wbytes = (size_t)(threads / 32) * kWarpBufAlloc + kWarpBufSlack;
-  uint32_t ns = pick_smem_slots(intv, hist, G, wbytes);
+  const size_t cur_bytes = T0.part_lg ? ((size_t)4 << T0.part_lg) : 0;     // partition cursors, after the warp buffers
+  uint32_t ns = pick_smem_slots(intv, hist, G, wbytes + cur_bytes);
   size_t smem = (((size_t)ns * smem_slot_bytes(intv, hist) + 15) & ~(size_t)15) + wbytes;
+  DevTables T = T0;
+  T.part_smem_off = (uint32_t)smem;
+  smem += cur_bytes;
   uint32_t grid = (uint32_t)G.sms;
   uint32_t need = (n + threads - 1) / threads;
   if (need < grid) grid = need;
@@ -1298,18 +1410,36 @@ cudaError_t launch_decode(const DevSchema& S, const LaunchGeom& G, const uint8_t
   return cudaGetLastError();
 }
 
-cudaError_t launch_process_columns(const DevSchema& S, const DevTables& T, const LaunchGeom& G,
+cudaError_t launch_process_columns(const DevSchema& S, const DevTables& T0, const LaunchGeom& G,
                                    const uint64_t* kh, const uint64_t* ts, const double* val,
                                    uint64_t n, cudaStream_t st, int* launches) {
   if (n == 0) return cudaSuccess;
   const bool hist = (S.ops & BH_OP_HIST) != 0;
-  uint32_t ns = pick_smem_slots(false, hist, G, 0);
+  const size_t cur_bytes = T0.part_lg ? ((size_t)4 << T0.part_lg) : 0;
+  uint32_t ns = pick_smem_slots(false, hist, G, cur_bytes);
   size_t smem = (size_t)ns * smem_slot_bytes(false, hist) + 16;
+  DevTables T = T0;
+  T.part_smem_off = (uint32_t)smem;
+  smem += cur_bytes;
   uint64_t grid = (uint64_t)G.sms;
   uint64_t need = (n + kColThreads - 1) / kColThreads;
   if (need < grid) grid = need;
   uint64_t chunk = (n + grid - 1) / grid;
   k_process_columns<<<(uint32_t)grid, kColThreads, smem, st>>>(S, T, kh, ts, val, n, chunk, ns);
+  if (launches) (*launches)++;
+  return cudaGetLastError();
+}
+
+// partitioned mode: fold every logged tuple into the tables and empty the log
+// intv: every logged value is an int32 (the log holds only events of an integer-valued raw schema): integer shared table
+cudaError_t launch_part_drain(const DevSchema& S, const DevTables& T, const LaunchGeom& G, bool intv, cudaStream_t st, int* launches) {
+  if (!T.part_lg) return cudaSuccess;
+  const bool hist = (S.ops & BH_OP_HIST) != 0;
+  const uint32_t ns = pick_smem_slots(intv, hist, G, 0);
+  const size_t smem = (size_t)ns * smem_slot_bytes(intv, hist) + 16;
+  const uint32_t grid = min((uint32_t)G.sms, 1u << T.part_lg);
+  if (intv) k_part_drain<true><<<grid, kDrainThreads, smem, st>>>(S, T, ns);
+  else k_part_drain<false><<<grid, kDrainThreads, smem, st>>>(S, T, ns);
   if (launches) (*launches)++;
   return cudaGetLastError();
 }
@@ -1390,6 +1520,7 @@ cudaError_t launch_init_tables(const DevTables& T, cudaStream_t st) {
   if ((e = cudaMemsetAsync(T.stats, 0, rows * sizeof(Stat), st)) != cudaSuccess) return e;
   if (T.hist && (e = cudaMemsetAsync(T.hist, 0, rows * T.hist_buckets * 4, st)) != cudaSuccess) return e;
   if ((e = cudaMemsetAsync(T.ring_win, 0xFF, (size_t)T.ring * 8, st)) != cudaSuccess) return e;
+  if (T.part_lg && (e = cudaMemsetAsync(T.part_fill, 0, ((size_t)T.part_ctas << T.part_lg) * 4, st)) != cudaSuccess) return e;   // logged tuples are dropped with the tables
   return cudaMemsetAsync(T.counters, 0, 8 * 8, st);
 }
 

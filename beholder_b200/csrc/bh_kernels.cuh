@@ -22,6 +22,8 @@ cudaError_t launch_process_raw(const DevSchema& S, const DevTables& T, const Lau
 cudaError_t launch_process_columns(const DevSchema& S, const DevTables& T, const LaunchGeom& G,
                                    const uint64_t* kh, const uint64_t* ts, const double* val,
                                    uint64_t n, cudaStream_t st, int* launches);
+// partitioned mode (DevTables::part_*): fold the logged tuples into the tables, empty the log
+cudaError_t launch_part_drain(const DevSchema& S, const DevTables& T, const LaunchGeom& G, bool intv, cudaStream_t st, int* launches);
 // decode only -> columns
 cudaError_t launch_decode(const DevSchema& S, const LaunchGeom& G, const uint8_t* payload,
                           const uint32_t* offsets, uint32_t n, uint64_t* kh, double* val,

@@ -87,7 +87,8 @@ typedef struct bh_config {
                                 * (checked by bh_poll_committed and by the completion thread); 0 -> 5 ms,
                                 * BH_NO_BATCH_DEADLINE -> only when full / bh_submit / bh_flush.  Bounds the ack
                                 * latency of index.js:151,154 under the prefetch limit of index.js:43. */
-  uint32_t reserved0;
+  uint32_t part_region_tuples; /* partitioned aggregation (BH_F_PARTITIONED): 16-byte tuples per (SM, partition) log
+                                * region; 0 -> 512.  The log takes SMs x partitions x this x 16 bytes of HBM. */
 } bh_config;
 #define BH_NO_BATCH_DEADLINE 0xFFFFFFFFu
 
@@ -96,6 +97,15 @@ enum {
   BH_F_GENERIC_KERNELS = 1,    /* never launch the fused kernel that has the reference's own schema compiled in
                                 * (api.TelemetryProgress keyed by mediaId + status, int32 progress): same results,
                                 * slower; for tests.  The environment variable BEHOLDER_GENERIC_KERNELS=1 does the same. */
+  BH_F_PARTITIONED = 4,        /* large key sets (BASELINE.json configs 3 and 4; no counterpart in the reference, whose
+                                * counter has a handful of labels, index.js:136-138): events that miss the per-SM
+                                * shared-memory table are logged as 16-byte tuples partitioned by table slot and folded
+                                * into the HBM tables later, one partition per SM, instead of one random HBM update per
+                                * event.  Same results.  On by itself when table_capacity >= 2^18; this flag forces it
+                                * for smaller tables, BH_F_NO_PARTITION keeps it off.  While it is on, launches that feed
+                                * one context must be issued on one stream at a time (the library re-orders itself
+                                * across a change of stream), and reads (snapshot, export, counters) fold the log first. */
+  BH_F_NO_PARTITION = 8,
   BH_F_NO_NUMA_BIND = 2        /* by default the pinned ingest ring (and bh_host_alloc buffers) are allocated while the
                                 * calling thread is confined to the CPUs of the GPU's NUMA node, and the thread's
                                 * affinity is restored afterwards; this flag (or BEHOLDER_NO_NUMA_BIND=1) turns it off */
