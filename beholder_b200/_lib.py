@@ -111,6 +111,8 @@ PROTOTYPES = {
     "bh_export_window_device": (C.c_int, [C.c_void_p, C.c_uint64, C.c_uint32, C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint64, _u64p, C.c_void_p]),
     "bh_export_window_static": (C.c_int, [C.c_void_p, C.c_uint64, C.c_uint32, C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint64, _u64p, C.c_void_p]),
     "bh_reset_device": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "bh_close_window_device": (C.c_int, [C.c_void_p, C.c_uint64, C.c_void_p]),
+    "bh_drain_device": (C.c_int, [C.c_void_p, C.c_void_p]),
     "bh_merge_records_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p]),
     "bh_sync": (C.c_int, [C.c_void_p]),
     "bh_synth_event_size": (C.c_uint32, [C.POINTER(BhSynthConfig), C.c_uint64, _u64p]),
@@ -143,8 +145,32 @@ PROTOTYPES.update({
     "bh_amqp_last_error": (C.c_char_p, [C.c_void_p]),
 })
 
+PROTOTYPES.update({
+    "bh_merge_blocks_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint64, _u64p, C.c_void_p]),
+    "bh_stream": (C.c_void_p, [C.c_void_p]),
+    "bh_stream_wait": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "bh_create_group": (C.c_int, [C.POINTER(BhConfig), C.POINTER(BhConfig), C.POINTER(C.c_int), C.c_uint32, C.c_uint64, C.POINTER(C.c_void_p)]),
+    "bh_group_destroy": (None, [C.c_void_p]),
+    "bh_group_size": (C.c_uint32, [C.c_void_p]),
+    "bh_group_local": (C.c_void_p, [C.c_void_p, C.c_uint32]),
+    "bh_group_owned": (C.c_void_p, [C.c_void_p, C.c_uint32]),
+    "bh_group_member": (C.c_void_p, [C.c_void_p, C.c_uint32]),
+    "bh_group_close_window": (C.c_int, [C.c_void_p, C.c_uint64]),
+    "bh_group_sync": (C.c_int, [C.c_void_p]),
+    "bh_group_last_error": (C.c_char_p, []),
+    "bh_member_create": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_uint32, C.c_uint32, C.c_uint64, C.c_uint32, C.POINTER(C.c_void_p)]),
+    "bh_member_destroy": (None, [C.c_void_p]),
+    "bh_member_ipc_handle": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "bh_member_connect_ipc": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "bh_member_connect_ptrs": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p)]),
+    "bh_member_area": (C.c_void_p, [C.c_void_p]),
+    "bh_member_close_window": (C.c_int, [C.c_void_p, C.c_uint64, C.c_void_p]),
+    "bh_member_check": (C.c_int, [C.c_void_p, _u64p]),
+})
+
 # test hooks that are not part of the public header
-_EXTRA = {"bh_debug_div64": (C.c_uint64, [C.c_uint64, C.c_uint64])}
+_EXTRA = {"bh_debug_div64": (C.c_uint64, [C.c_uint64, C.c_uint64]),
+          "bh_debug_push_each": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32])}
 
 
 class BeholderError(RuntimeError):

@@ -67,6 +67,7 @@ struct bh_ctx {
   bool part_f64_tuples = false;                   // the log holds values that did not come from an int32 field
   cudaStream_t part_stream = nullptr;
   cudaEvent_t part_ev = nullptr;
+  cudaEvent_t wait_ev = nullptr;                  // bh_stream_wait
   std::string err;
   // One lock around every entry point: the producer thread (the Node main thread / the asyncio loop) and the
   // library's own completion thread are the two parties.  Recursive because entry points call each other.
@@ -265,6 +266,24 @@ int submit_current(bh_ctx* c) {
   s.n = 0; s.bytes = 0; s.h_offsets[0] = 0;
   c->cur = (c->cur + 1) % (uint32_t)c->slabs.size();
   return slab_acquire(c, c->cur);
+}
+
+// Large host-to-ring copies run on a few threads: one core moves 10-15 GB/s, a PCIe Gen5 x16 link takes 55, so a
+// single-threaded memcpy in front of the H2D copy would be the bottleneck of bh_push_batch from ordinary
+// (pageable) memory.  Threads are started per copy (tens of microseconds against milliseconds of copying).
+void ring_copy(uint8_t* dst, const uint8_t* src, size_t n) {
+  constexpr size_t kParallelFrom = 8u << 20;
+  static const unsigned hw = std::max(1u, std::thread::hardware_concurrency());
+  const unsigned nt = n < kParallelFrom ? 1u : std::min<unsigned>({8u, std::max(1u, hw / 2), (unsigned)(n / (2u << 20))});
+  if (nt <= 1) { memcpy(dst, src, n); return; }
+  std::vector<std::thread> th;
+  const size_t part = ((n + nt - 1) / nt + 4095) & ~(size_t)4095;
+  for (unsigned i = 1; i < nt; i++) {
+    const size_t lo = std::min(n, (size_t)i * part), hi = std::min(n, lo + part);
+    if (hi > lo) th.emplace_back([=] { memcpy(dst + lo, src + lo, hi - lo); });
+  }
+  memcpy(dst, src, std::min(n, part));
+  for (auto& t : th) t.join();
 }
 
 // the partial slab just received its first message: start its deadline, wake the completion thread
@@ -515,6 +534,7 @@ void bh_destroy(bh_ctx* c) {
   if (c->T.part_tuples) cudaFree(c->T.part_tuples);
   if (c->T.part_fill) cudaFree(c->T.part_fill);
   if (c->part_ev) cudaEventDestroy(c->part_ev);
+  if (c->wait_ev) cudaEventDestroy(c->wait_ev);
   if (c->d_owner_counts) cudaFree(c->d_owner_counts);
   if (c->d_owner_cursor) cudaFree(c->d_owner_cursor);
   if (c->d_export) cudaFree(c->d_export);
@@ -583,7 +603,7 @@ int bh_push_batch(bh_ctx* c, const uint8_t* slab, const uint32_t* off, const uin
       if (off[k + 1] < off[k]) return fail(c, BH_ERR_INVALID, "offsets not monotone at %u", k);
     uint64_t nb = off[j] - off[i];
     if (s->n == 0) slab_first_message(c);
-    memcpy(s->h_payload + s->bytes, slab + off[i], nb);
+    ring_copy(s->h_payload + s->bytes, slab + off[i], nb);
     for (uint32_t k = i; k < j; k++) {
       s->h_offsets[s->n + (k - i) + 1] = (uint32_t)(s->bytes + (off[k + 1] - off[i]));
       s->h_ts[s->n + (k - i)] = ts ? ts[k] : 0;
@@ -927,6 +947,23 @@ int bh_export_window_static(bh_ctx* c, uint64_t window_id, uint32_t n_owners, bh
   return BH_OK;
 }
 
+int bh_close_window_device(bh_ctx* c, uint64_t window_id, void* stream) {
+  if (!c) return BH_ERR_INVALID;
+  BH_LOCK(c);
+  DeviceGuard guard(c->device);
+  cudaStream_t st = stream ? (cudaStream_t)stream : c->st_compute;
+  { int rc = part_drain(c, st); if (rc) return rc; }
+  CU(c, launch_close_window(c->T, window_id, st));
+  return BH_OK;
+}
+
+int bh_drain_device(bh_ctx* c, void* stream) {
+  if (!c) return BH_ERR_INVALID;
+  BH_LOCK(c);
+  DeviceGuard guard(c->device);
+  return part_drain(c, stream ? (cudaStream_t)stream : c->st_compute);
+}
+
 int bh_reset_device(bh_ctx* c, void* stream) {
   if (!c) return BH_ERR_INVALID;
   BH_LOCK(c);
@@ -936,8 +973,8 @@ int bh_reset_device(bh_ctx* c, void* stream) {
     CU(c, cudaEventRecord(c->part_ev, c->part_stream));
     CU(c, cudaStreamWaitEvent(st, c->part_ev, 0));
   }
-  c->part_pending = 0; c->part_f64_tuples = false;                  // launch_init_tables empties the log as well
-  CU(c, launch_init_tables(c->T, st));
+  c->part_pending = 0; c->part_f64_tuples = false;                  // the reset empties the log as well
+  CU(c, launch_reset_tables(c->T, st));
   return BH_OK;
 }
 
@@ -947,6 +984,38 @@ int bh_merge_records_device(bh_ctx* c, const bh_record* d_records, const uint32_
   DeviceGuard guard(c->device);
   cudaStream_t st = stream ? (cudaStream_t)stream : c->st_compute;
   CU(c, launch_merge(c->S, c->T, d_records, d_hist, n, st));
+  return BH_OK;
+}
+
+int bh_merge_blocks_device(bh_ctx* c, const bh_record* d_records, const uint32_t* d_hist, uint32_t n_blocks,
+                           uint64_t block_stride, const uint64_t* d_block_counts, void* stream) {
+  if (!c || (n_blocks && (!d_records || !d_block_counts))) return fail(c, BH_ERR_INVALID, "null argument");
+  BH_LOCK(c);
+  DeviceGuard guard(c->device);
+  cudaStream_t st = stream ? (cudaStream_t)stream : c->st_compute;
+  CU(c, launch_merge_blocks(c->S, c->T, d_records, d_hist, n_blocks, block_stride, (const unsigned long long*)d_block_counts, st));
+  return BH_OK;
+}
+
+void* bh_stream(bh_ctx* c) { return c ? (void*)c->st_compute : nullptr; }
+
+int bh_stream_wait(bh_ctx* c, void* stream) {
+  if (!c) return BH_ERR_INVALID;
+  BH_LOCK(c);
+  DeviceGuard guard(c->device);
+  if ((cudaStream_t)stream == c->st_compute) return BH_OK;
+  if (!c->wait_ev) CU(c, cudaEventCreateWithFlags(&c->wait_ev, cudaEventDisableTiming));
+  CU(c, cudaEventRecord(c->wait_ev, (cudaStream_t)stream));
+  CU(c, cudaStreamWaitEvent(c->st_compute, c->wait_ev, 0));
+  return BH_OK;
+}
+
+// test / bench hook: bh_push once per message, driven from C (what the N-API shim does for each rmsg.message.content)
+int bh_debug_push_each(bh_ctx* c, const uint8_t* slab, const uint32_t* off, const uint64_t* ts, uint32_t n) {
+  for (uint32_t i = 0; i < n; i++) {
+    int rc = bh_push(c, slab + off[i], off[i + 1] - off[i], ts ? ts[i] : 0);
+    if (rc != BH_OK) return rc;
+  }
   return BH_OK;
 }
 

@@ -256,8 +256,10 @@ __device__ __forceinline__ void aggregate_event(const DevSchema& S, const DevTab
     } else {
       const uint64_t ord = f64_order((uint64_t)__double_as_longlong(v));
       if (ops & BH_OP_SUM) atomicAdd(M.fsum() + slot, v);
-      if (ops & BH_OP_MIN) atomicMax(M.fmin_inv() + slot, (unsigned long long)~ord);
-      if (ops & BH_OP_MAX) atomicMax(M.fmax_ord() + slot, (unsigned long long)ord);
+      // both columns only ever grow: a plain read that already shows a value at least as large makes the
+      // (CAS-loop) atomic unnecessary, and after a key's first few events that is the usual case
+      if ((ops & BH_OP_MIN) && (unsigned long long)~ord > M.fmin_inv()[slot]) atomicMax(M.fmin_inv() + slot, (unsigned long long)~ord);
+      if ((ops & BH_OP_MAX) && (unsigned long long)ord > M.fmax_ord()[slot]) atomicMax(M.fmax_ord() + slot, (unsigned long long)ord);
     }
     C.ok++;
     return;
@@ -914,6 +916,13 @@ __device__ __forceinline__ uint4 ldg_stream(const uint4* p) {
   asm("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
   return v;
 }
+// the same load pinned to its place in the instruction stream (software pipelining: a plain asm may be sunk to its
+// first use, which turns "load the next chunk, then work on this one" back into "wait for every chunk")
+__device__ __forceinline__ uint4 ldg_stream_here(const uint4* p) {
+  uint4 v;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+  return v;
+}
 constexpr uint32_t kPrefetchAhead = 4;   // batches ahead whose cache lines are pulled into L2
 __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" :: "l"(p)); }
 
@@ -1168,48 +1177,84 @@ k_process_columns(const __grid_constant__ DevSchema S, const __grid_constant__ D
 // only this CTA is touching.  Histogram buckets go to the HBM rows directly (one L2 atomic per tuple): the
 // slice's rows stay in L2 while the partition is being drained.
 constexpr int kDrainThreads = 1024;
+constexpr uint32_t kDrainMaxCtas = 256;       // regions per partition (= SMs of the device that logged them)
 __shared__ unsigned long long g_wmin;
+__shared__ uint32_t g_fill[kDrainMaxCtas];
+__shared__ uint32_t g_next;
 
 template <bool INTV>
 __global__ void __launch_bounds__(kDrainThreads, 1)
 k_part_drain(const __grid_constant__ DevSchema S, const __grid_constant__ DevTables T, uint32_t ns) {
   const bool hist = (S.ops & BH_OP_HIST) != 0;
   const SmemTable M = smem_table_carve<INTV>(ns, hist);
+  // window id of every ring slot, after the table (a tuple names its window by ring slot)
+  unsigned long long* ringwin = (unsigned long long*)(g_smem + (((size_t)ns * smem_slot_bytes(INTV, hist) + 15) & ~(size_t)15));
   if (threadIdx.x == 0) g_wmin = kNoWindow;
   if (threadIdx.x < 8) g_cnt[threadIdx.x] = 0;
   __syncthreads();
   for (uint32_t r = threadIdx.x; r < T.ring; r += blockDim.x) {
     const unsigned long long w = T.ring_win[r];
+    ringwin[r] = w;
     if (w != kNoWindow) atomicMin(&g_wmin, w);
   }
   __syncthreads();
   const uint64_t wbase = g_wmin == kNoWindow || g_wmin == 0 ? 0 : g_wmin - 1;
   const uint32_t P = 1u << T.part_lg, sh = 64u - T.part_lg;
-  const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+  const uint32_t lane = threadIdx.x & 31;
+  const uint32_t ctas = min(T.part_ctas, kDrainMaxCtas);
+  const uint64_t slice = T.cap >> T.part_lg;                     // table slots of one partition (0: table smaller than P)
   LaneCounters C{0u};
   for (uint32_t p = blockIdx.x; p < P; p += gridDim.x) {
     smem_table_clear<INTV>(M);
-    __syncthreads();
-    for (uint32_t c = warp; c < T.part_ctas; c += nwarps) {            // a warp takes whole regions
-      const uint64_t region = ((uint64_t)c << T.part_lg) | p;
-      const uint32_t n = min(T.part_fill[region], T.part_cap);
-      const uint4* src = T.part_tuples + region * T.part_cap;
-      for (uint32_t i0 = 0; i0 < n; i0 += 32) {
-        const bool valid = i0 + lane < n;
-        const uint32_t mask = __ballot_sync(0xFFFFFFFFu, valid);
-        if (!valid) continue;
-        const uint4 t = ldg_stream(src + i0 + lane);
-        const uint64_t a = ((uint64_t)t.y << 32) | t.x, vbits = ((uint64_t)t.w << 32) | t.z;
-        const uint32_t r = (uint32_t)(a >> sh);
-        const uint64_t kh = ((a & ((1ull << sh) - 1)) | ((uint64_t)p << sh)) * kHashMulInv;
-        const uint64_t win = T.ring_win[r];
-        const double v = __longlong_as_double((long long)vbits);
-        aggregate_event<INTV, false>(S, T, M, kh, win, wbase, v, INTV ? (int32_t)v : 0, C, mask);
+    for (uint32_t c = threadIdx.x; c < ctas; c += blockDim.x) g_fill[c] = min(T.part_fill[((uint64_t)c << T.part_lg) | p], T.part_cap);
+    if (threadIdx.x == 0) g_next = 0;
+    // The partition's slice of every open window's key and stat columns is pulled into L2 now: the look-ups of
+    // the flush (and of the inserts, with histograms) then cost an L2 hit instead of a DRAM round trip each.
+    // A slice is contiguous: partition = the top bits of the slot index.
+    {
+      const uint64_t lines_k = (slice * 8 + 127) / 128, lines_s = (slice * sizeof(Stat) + 127) / 128;
+      for (uint32_t r = 0; r < T.ring; r++) {
+        if (ringwin[r] == kNoWindow) continue;
+        const uint8_t* kb = (const uint8_t*)(T.keys + (uint64_t)r * T.stride + (uint64_t)p * slice);
+        const uint8_t* sb = (const uint8_t*)(T.stats + (uint64_t)r * T.stride + (uint64_t)p * slice);
+        for (uint64_t i = threadIdx.x; i < lines_k + lines_s; i += blockDim.x)
+          prefetch_l2(i < lines_k ? kb + i * 128 : sb + (i - lines_k) * 128);
       }
     }
     __syncthreads();
+    // Warps take whole regions, handed out by a shared counter (regions differ in fill), 32 tuples at a time; the
+    // next 32 are already in flight while the current ones are aggregated.
+    auto grab = [&]() { uint32_t v = 0; if (lane == 0) v = atomicAdd(&g_next, 1u); return __shfl_sync(0xFFFFFFFFu, v, 0); };
+    auto next_pos = [&](uint32_t& c, uint32_t& i0) { while (c < ctas && i0 >= g_fill[c]) { c = grab(); i0 = 0; } };
+    auto load = [&](uint32_t c, uint32_t i0, bool& valid) {
+      uint4 t = make_uint4(0, 0, 0, 0);
+      valid = c < ctas && i0 + lane < g_fill[c];
+      if (valid) t = ldg_stream_here(T.part_tuples + (((uint64_t)c << T.part_lg) | p) * T.part_cap + i0 + lane);
+      return t;
+    };
+    uint32_t c = grab(), i0 = 0;
+    next_pos(c, i0);
+    bool valid;
+    uint4 t = load(c, i0, valid);
+    while (c < ctas) {
+      uint32_t nc = c, ni = i0 + 32;
+      next_pos(nc, ni);
+      bool nvalid;
+      const uint4 nt = load(nc, ni, nvalid);
+      const uint32_t mask = __ballot_sync(0xFFFFFFFFu, valid);
+      if (valid) {
+        const uint64_t a = ((uint64_t)t.y << 32) | t.x, vbits = ((uint64_t)t.w << 32) | t.z;
+        const uint64_t kh = ((a & ((1ull << sh) - 1)) | ((uint64_t)p << sh)) * kHashMulInv;
+        const uint64_t win = ringwin[(uint32_t)(a >> sh)];
+        const double v = __longlong_as_double((long long)vbits);
+        aggregate_event<INTV, false>(S, T, M, kh, win, wbase, v, INTV ? (int32_t)v : 0, C, mask);
+      }
+      __syncwarp();
+      c = nc; i0 = ni; t = nt; valid = nvalid;
+    }
+    __syncthreads();
     smem_table_flush<INTV>(S, T, M, wbase);
-    for (uint32_t c = threadIdx.x; c < T.part_ctas; c += blockDim.x) T.part_fill[((uint64_t)c << T.part_lg) | p] = 0;
+    for (uint32_t cc = threadIdx.x; cc < T.part_ctas; cc += blockDim.x) T.part_fill[((uint64_t)cc << T.part_lg) | p] = 0;
     __syncthreads();
   }
   // the tuples were counted as aggregated when they were logged: only what was refused now moves to the drop counters
@@ -1222,11 +1267,17 @@ k_part_drain(const __grid_constant__ DevSchema S, const __grid_constant__ DevTab
 // =========================================================================================
 // window close: export (compact by owner), merge, recycle
 // =========================================================================================
+// Liveness is decided from the key column (8 bytes per slot, streamed) so that a close or an export of a large,
+// sparsely filled table reads the 32-byte stat rows of live slots only.
 __device__ __forceinline__ bool export_row(const DevTables& T, uint64_t base, uint64_t slot, uint64_t* key) {
-  const Stat* s = T.stats + base + slot;
-  if (s->count == 0) return false;
-  *key = slot >= T.cap ? (slot == T.cap ? kLockKey : kEmptyKey) : T.keys[base + slot];
-  return true;
+  if (slot < T.cap) {
+    const unsigned long long k = T.keys[base + slot];
+    if (k == kEmptyKey) return false;
+    *key = k;
+  } else {
+    *key = slot == T.cap ? kLockKey : kEmptyKey;        // the two side slots have no key cell
+  }
+  return T.stats[base + slot].count != 0;
 }
 
 // win == kNoWindow exports every open window.  Rows are visited ring slot by ring slot.
@@ -1265,36 +1316,68 @@ __global__ void k_export_prefix(uint32_t n_owners, const unsigned long long* own
   }
 }
 
-__global__ void k_export_scatter(const __grid_constant__ DevSchema S, const __grid_constant__ DevTables T, uint64_t win,
-                                 uint32_t owner_shift, bh_record* out, uint32_t* hist_out, uint64_t cap,
-                                 unsigned long long* cursor, uint64_t owner_stride,
-                                 const unsigned long long* peer_base, const unsigned long long* peer_hist_base,
-                                 uint32_t my_rank) {
+// counts from the cursors of a single-pass export (cursor[o] started at o * owner_stride)
+__global__ void k_export_counts(uint32_t n_owners, const unsigned long long* cursor, unsigned long long* owner_counts,
+                                uint64_t owner_stride) {
+  for (uint32_t o = blockIdx.x * blockDim.x + threadIdx.x; o < n_owners; o += gridDim.x * blockDim.x)
+    owner_counts[o] = cursor[o] - (unsigned long long)o * owner_stride;
+}
+
+// One warp looks at 32 consecutive slots.  Output positions are claimed once per warp and owner (the lanes that
+// export to the same owner elect a leader), records are written by their lanes, histogram rows are copied by the
+// whole warp, one row at a time, so that both sides of the copy are coalesced.
+__global__ void __launch_bounds__(256)
+k_export_scatter(const __grid_constant__ DevSchema S, const __grid_constant__ DevTables T, uint64_t win,
+                 uint32_t owner_shift, bh_record* out, uint32_t* hist_out, uint64_t cap,
+                 unsigned long long* cursor, uint64_t owner_stride,
+                 const unsigned long long* peer_base, const unsigned long long* peer_hist_base,
+                 uint32_t my_rank) {
   uint64_t rows = (uint64_t)T.ring * T.stride, r0 = 0;
   if (win != kNoWindow) { r0 = (uint64_t)((uint32_t)win & (T.ring - 1)) * T.stride; rows = r0 + T.stride; }
-  for (uint64_t row = r0 + blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; row < rows; row += (uint64_t)gridDim.x * blockDim.x) {
-    uint64_t base, slot, w, key;
-    if (!export_pick(T, win, row, &base, &slot, &w)) continue;
-    if (!export_row(T, base, slot, &key)) continue;
-    uint32_t o = owner_shift >= 64 ? 0u : (uint32_t)(key >> owner_shift);
-    unsigned long long pos = atomicAdd(&cursor[o], 1ull);
-    if (pos >= cap || (owner_stride && pos >= (unsigned long long)(o + 1) * owner_stride)) continue;
-    const Stat s = T.stats[base + slot];
-    bh_record rec;
-    rec.key_hash = key; rec.window_id = w; rec.count = s.count;
-    rec.sum = (S.ops & BH_OP_SUM) ? s.sum : 0.0;
-    rec.min = (S.ops & BH_OP_MIN) && s.min_inv ? __longlong_as_double((long long)f64_unorder(~s.min_inv)) : 0.0;
-    rec.max = (S.ops & BH_OP_MAX) && s.max_ord ? __longlong_as_double((long long)f64_unorder(s.max_ord)) : 0.0;
-    // peer_base: owner o's receive buffer lives on GPU o (mapped peer memory, NVLink): the row goes straight
-    // into block `my_rank` of it -- the export IS the exchange, no staging copy and no all-to-all
-    const uint64_t peer_row = (uint64_t)my_rank * owner_stride + (pos - (unsigned long long)o * owner_stride);
-    if (peer_base) ((bh_record*)peer_base[o])[peer_row] = rec;
-    else out[pos] = rec;
-    uint32_t* hdst = peer_base ? (peer_hist_base ? (uint32_t*)peer_hist_base[o] + peer_row * T.hist_buckets : nullptr)
-                               : (hist_out ? hist_out + pos * T.hist_buckets : nullptr);
-    if (hdst && T.hist) {
-      const uint32_t* h = T.hist + (base + slot) * T.hist_buckets;
-      for (uint32_t b = 0; b < T.hist_buckets; b++) hdst[b] = h[b];
+  const uint32_t lane = threadIdx.x & 31;
+  const uint64_t step = (uint64_t)gridDim.x * blockDim.x;
+  for (uint64_t row0 = r0 + blockIdx.x * (uint64_t)blockDim.x + (threadIdx.x & ~31u); row0 < rows; row0 += step) {
+    const uint64_t row = row0 + lane;
+    uint64_t base = 0, slot = 0, w = 0, key = 0;
+    bool live = row < rows && export_pick(T, win, row, &base, &slot, &w) && export_row(T, base, slot, &key);
+    const uint32_t livemask = __ballot_sync(0xFFFFFFFFu, live);
+    if (!livemask) continue;
+    const uint32_t o = live && owner_shift < 64 ? (uint32_t)(key >> owner_shift) : 0u;
+    unsigned long long pos = 0;
+    if (live) {
+      const uint32_t peers = __match_any_sync(livemask, o);
+      const uint32_t leader = __ffs(peers) - 1;
+      unsigned long long first = 0;
+      if (lane == leader) first = atomicAdd(&cursor[o], (unsigned long long)__popc(peers));
+      first = __shfl_sync(peers, first, leader);
+      pos = first + __popc(peers & ((1u << lane) - 1));
+      if (pos >= cap || (owner_stride && pos >= (unsigned long long)(o + 1) * owner_stride)) live = false;   // cut: counted, not stored
+    }
+    uint32_t* hdst = nullptr;
+    if (live) {
+      const Stat s = T.stats[base + slot];
+      bh_record rec;
+      rec.key_hash = key; rec.window_id = w; rec.count = s.count;
+      rec.sum = (S.ops & BH_OP_SUM) ? s.sum : 0.0;
+      rec.min = (S.ops & BH_OP_MIN) && s.min_inv ? __longlong_as_double((long long)f64_unorder(~s.min_inv)) : 0.0;
+      rec.max = (S.ops & BH_OP_MAX) && s.max_ord ? __longlong_as_double((long long)f64_unorder(s.max_ord)) : 0.0;
+      // peer_base: owner o's receive buffer lives on GPU o (mapped peer memory, NVLink): the row goes straight
+      // into block `my_rank` of it -- the export IS the exchange, no staging copy and no all-to-all
+      const uint64_t peer_row = (uint64_t)my_rank * owner_stride + (pos - (unsigned long long)o * owner_stride);
+      if (peer_base) ((bh_record*)peer_base[o])[peer_row] = rec;
+      else out[pos] = rec;
+      hdst = peer_base ? (peer_hist_base ? (uint32_t*)peer_hist_base[o] + peer_row * T.hist_buckets : nullptr)
+                       : (hist_out ? hist_out + pos * T.hist_buckets : nullptr);
+    }
+    if (T.hist) {
+      uint32_t todo = __ballot_sync(0xFFFFFFFFu, hdst != nullptr);
+      while (todo) {
+        const uint32_t l = __ffs(todo) - 1;
+        todo &= todo - 1;
+        uint32_t* d = (uint32_t*)__shfl_sync(0xFFFFFFFFu, (unsigned long long)hdst, l);
+        const uint32_t* h = T.hist + (row0 + l) * T.hist_buckets;
+        for (uint32_t b = lane; b < T.hist_buckets; b += 32) d[b] = h[b];
+      }
     }
   }
 }
@@ -1322,17 +1405,79 @@ __global__ void k_merge(const __grid_constant__ DevSchema S, const __grid_consta
   if (dropped[1]) atomicAdd(&T.counters[C_WINDOW], (unsigned long long)dropped[1]);
 }
 
+// Rows received from other GPUs, one block per sender: block b holds min(counts[b], stride) valid rows at
+// [b * stride, ...).  Nothing past a block's count is read, so the receive buffer never needs clearing.
+// Loads bypass L1 (.cg): the rows were written by other GPUs over NVLink.
+__global__ void k_merge_blocks(const __grid_constant__ DevSchema S, const __grid_constant__ DevTables T,
+                               const bh_record* recs, const uint32_t* hist, uint32_t n_blocks, uint64_t stride,
+                               const unsigned long long* counts) {
+  uint32_t dropped[2] = {0, 0};
+  for (uint32_t b = 0; b < n_blocks; b++) {
+    const uint64_t n = min((uint64_t)__ldcg(&counts[b]), stride);
+    for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
+      const uint64_t row = (uint64_t)b * stride + i;
+      const unsigned long long* q = reinterpret_cast<const unsigned long long*>(recs + row);
+      bh_record rec;
+      rec.key_hash = __ldcg(q); rec.window_id = __ldcg(q + 1); rec.count = __ldcg(q + 2);
+      rec.sum = __longlong_as_double((long long)__ldcg(q + 3));
+      rec.min = __longlong_as_double((long long)__ldcg(q + 4));
+      rec.max = __longlong_as_double((long long)__ldcg(q + 5));
+      if (rec.count == 0) continue;
+      uint32_t r;
+      const uint32_t gs = g_find_or_insert(T, rec.window_id, rec.key_hash, &r);
+      if (gs >= kGslotWindow) { dropped[gs == kGslotFull ? 0 : 1] += 1; continue; }
+      const uint64_t gi = (uint64_t)r * T.stride + gs;
+      const uint64_t omin = f64_order((uint64_t)__double_as_longlong(rec.min));
+      const uint64_t omax = f64_order((uint64_t)__double_as_longlong(rec.max));
+      g_update(T, S.ops, gi, rec.count, rec.sum, ~omin, omax);
+      if (hist && T.hist)
+        for (uint32_t k = 0; k < T.hist_buckets; k++) {
+          const uint32_t h = __ldcg(&hist[row * T.hist_buckets + k]);
+          if (h) atomicAdd(&T.hist[gi * T.hist_buckets + k], h);
+        }
+    }
+  }
+  if (dropped[0]) atomicAdd(&T.counters[C_TABLE_FULL], (unsigned long long)dropped[0]);
+  if (dropped[1]) atomicAdd(&T.counters[C_WINDOW], (unsigned long long)dropped[1]);
+}
+
+// win == kNoWindow: every open window (bh_reset_device).  Only slots that hold a key are written: closing a
+// window costs 8 bytes read per slot plus the rows that were in use, not the whole table (histogram rows
+// included) every time.
 __global__ void k_close_clear(const __grid_constant__ DevTables T, uint64_t win) {
-  uint32_t r = (uint32_t)win & (T.ring - 1);
-  if (T.ring_win[r] != win) return;
-  uint64_t base = (uint64_t)r * T.stride;
-  for (uint64_t slot = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; slot < T.stride; slot += (uint64_t)gridDim.x * blockDim.x) {
-    T.keys[base + slot] = kEmptyKey;
-    T.stats[base + slot] = Stat{0ull, 0.0, 0ull, 0ull};
-    if (T.hist) for (uint32_t b = 0; b < T.hist_buckets; b++) T.hist[(base + slot) * T.hist_buckets + b] = 0;
+  uint64_t rows = (uint64_t)T.ring * T.stride, r0 = 0;
+  if (win != kNoWindow) {
+    const uint32_t r = (uint32_t)win & (T.ring - 1);
+    if (T.ring_win[r] != win) return;
+    r0 = (uint64_t)r * T.stride; rows = r0 + T.stride;
+  }
+  for (uint64_t row = r0 + blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; row < rows; row += (uint64_t)gridDim.x * blockDim.x) {
+    const uint32_t r = (uint32_t)(row / T.stride);
+    const uint64_t slot = row - (uint64_t)r * T.stride;
+    if (T.ring_win[r] == kNoWindow) continue;             // a free ring slot is clean already
+    if (slot < T.cap) {
+      if (T.keys[row] == kEmptyKey) continue;
+      T.keys[row] = kEmptyKey;
+    } else if (T.stats[row].count == 0) {
+      continue;
+    }
+    T.stats[row] = Stat{0ull, 0.0, 0ull, 0ull};
+    if (T.hist) {
+      uint4* h = reinterpret_cast<uint4*>(T.hist + row * T.hist_buckets);
+      if ((T.hist_buckets & 3u) == 0) for (uint32_t b = 0; b < T.hist_buckets / 4; b++) h[b] = make_uint4(0, 0, 0, 0);
+      else for (uint32_t b = 0; b < T.hist_buckets; b++) T.hist[row * T.hist_buckets + b] = 0;
+    }
   }
 }
-__global__ void k_close_release(const __grid_constant__ DevTables T, uint64_t win) {
+__global__ void k_close_release(const __grid_constant__ DevTables T, uint64_t win, bool reset) {
+  if (win == kNoWindow) {                                 // every ring slot; reset: also the counters and the tuple log
+    const uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x, step = (uint64_t)gridDim.x * blockDim.x;
+    for (uint64_t r = i; r < T.ring; r += step) T.ring_win[r] = kNoWindow;
+    if (!reset) return;
+    if (i < 8) T.counters[i] = 0;
+    if (T.part_lg) for (uint64_t q = i; q < ((uint64_t)T.part_ctas << T.part_lg); q += step) T.part_fill[q] = 0;
+    return;
+  }
   uint32_t r = (uint32_t)win & (T.ring - 1);
   if (blockIdx.x == 0 && threadIdx.x == 0 && T.ring_win[r] == win) T.ring_win[r] = kNoWindow;
 }
@@ -1342,14 +1487,18 @@ __global__ void k_close_release(const __grid_constant__ DevTables T, uint64_t wi
 // =========================================================================================
 // once per device, with that device current (bh_create)
 cudaError_t configure_kernels(const LaunchGeom& G) {
-  int dyn = G.smem_optin - 1024;   // leave room for the kernels' static shared memory
   const void* fns[] = {(const void*)k_process_raw<true, false, 0>, (const void*)k_process_raw<true, true, 0>,
                        (const void*)k_process_raw<false, false, 0>, (const void*)k_process_raw<false, true, 0>,
                        (const void*)k_process_raw<true, false, 1>, (const void*)k_process_raw<true, false, 2>,
                        (const void*)k_decode<false>, (const void*)k_decode<true>, (const void*)k_process_columns,
                        (const void*)k_part_drain<true>, (const void*)k_part_drain<false>};
   for (const void* f : fns) {
-    cudaError_t e = cudaFuncSetAttribute(f, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn);
+    cudaFuncAttributes at;
+    cudaError_t e = cudaFuncGetAttributes(&at, f);
+    if (e != cudaSuccess) return e;
+    // everything the SM offers beyond the kernel's own static shared memory (pick_smem_slots keeps 1 KB + the
+    // static arrays of the drain kernel clear of it)
+    e = cudaFuncSetAttribute(f, cudaFuncAttributeMaxDynamicSharedMemorySize, G.smem_optin - (int)at.sharedSizeBytes);
     if (e != cudaSuccess) return e;
   }
   return cudaSuccess;
@@ -1435,8 +1584,9 @@ cudaError_t launch_process_columns(const DevSchema& S, const DevTables& T0, cons
 cudaError_t launch_part_drain(const DevSchema& S, const DevTables& T, const LaunchGeom& G, bool intv, cudaStream_t st, int* launches) {
   if (!T.part_lg) return cudaSuccess;
   const bool hist = (S.ops & BH_OP_HIST) != 0;
-  const uint32_t ns = pick_smem_slots(intv, hist, G, 0);
-  const size_t smem = (size_t)ns * smem_slot_bytes(intv, hist) + 16;
+  const size_t ring_bytes = (size_t)T.ring * 8;
+  const uint32_t ns = pick_smem_slots(intv, hist, G, ring_bytes + 2048);     // + the kernel's static arrays
+  const size_t smem = (((size_t)ns * smem_slot_bytes(intv, hist) + 15) & ~(size_t)15) + ring_bytes;
   const uint32_t grid = min((uint32_t)G.sms, 1u << T.part_lg);
   if (intv) k_part_drain<true><<<grid, kDrainThreads, smem, st>>>(S, T, ns);
   else k_part_drain<false><<<grid, kDrainThreads, smem, st>>>(S, T, ns);
@@ -1461,10 +1611,14 @@ cudaError_t launch_export(const DevSchema& S, const DevTables& T, uint64_t windo
   uint64_t rows = window_id == kNoWindow ? (uint64_t)T.ring * T.stride : T.stride;
   uint64_t blocks = (rows + 255) / 256;
   if (blocks > 148 * 8) blocks = 148 * 8;
-  k_export_count<<<(uint32_t)blocks, 256, 0, st>>>(T, window_id, shift, owner_counts);
+  // rows packed by owner need every owner's count before the first row can be placed: two passes.  One owner, or
+  // owners at a fixed stride: one pass, the counts are read off the cursors afterwards.
+  const bool two_pass = n_owners > 1 && owner_stride == 0;
+  if (two_pass) k_export_count<<<(uint32_t)blocks, 256, 0, st>>>(T, window_id, shift, owner_counts);
   k_export_prefix<<<1, 32, 0, st>>>(n_owners, owner_counts, owner_cursor, owner_stride);
   k_export_scatter<<<(uint32_t)blocks, 256, 0, st>>>(S, T, window_id, shift, out, hist_out, cap, owner_cursor, owner_stride,
                                                      peer_base, peer_hist_base, my_rank);
+  if (!two_pass) k_export_counts<<<(n_owners + 255) / 256, 256, 0, st>>>(n_owners, owner_cursor, owner_counts, owner_stride);
   return cudaGetLastError();
 }
 
@@ -1505,11 +1659,28 @@ cudaError_t launch_merge(const DevSchema& S, const DevTables& T, const bh_record
   return cudaGetLastError();
 }
 
-cudaError_t launch_close_window(const DevTables& T, uint64_t window_id, cudaStream_t st) {
-  uint64_t blocks = (T.stride + 255) / 256;
+cudaError_t launch_merge_blocks(const DevSchema& S, const DevTables& T, const bh_record* recs, const uint32_t* hist,
+                                uint32_t n_blocks, uint64_t stride, const unsigned long long* counts, cudaStream_t st) {
+  if (n_blocks == 0 || stride == 0) return cudaSuccess;
+  uint64_t blocks = (stride + 255) / 256;
   if (blocks > 148 * 8) blocks = 148 * 8;
-  k_close_clear<<<(uint32_t)blocks, 256, 0, st>>>(T, window_id);
-  k_close_release<<<1, 32, 0, st>>>(T, window_id);
+  k_merge_blocks<<<(uint32_t)blocks, 256, 0, st>>>(S, T, recs, hist, n_blocks, stride, counts);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_close_window(const DevTables& T, uint64_t window_id, cudaStream_t st) {
+  uint64_t blocks = ((window_id == kNoWindow ? T.stride * T.ring : T.stride) + 255) / 256;
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  k_close_clear<<<(uint32_t)blocks, 256, 0, st>>>(T, window_id);       // kNoWindow: every open window
+  k_close_release<<<1, 256, 0, st>>>(T, window_id, false);
+  return cudaGetLastError();
+}
+
+// bh_reset_device: close every open window, zero the counters, empty the tuple log -- O(slots that hold a key),
+// where launch_init_tables (used once, on fresh memory) writes every byte of every table
+cudaError_t launch_reset_tables(const DevTables& T, cudaStream_t st) {
+  k_close_clear<<<148 * 8, 256, 0, st>>>(T, kNoWindow);
+  k_close_release<<<148, 256, 0, st>>>(T, kNoWindow, true);
   return cudaGetLastError();
 }
 

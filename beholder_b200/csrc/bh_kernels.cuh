@@ -39,7 +39,10 @@ cudaError_t launch_export_static(const DevSchema& S, const DevTables& T, uint64_
                                  unsigned long long* owner_counts, cudaStream_t st);
 cudaError_t launch_merge(const DevSchema& S, const DevTables& T, const bh_record* recs,
                          const uint32_t* hist, uint64_t n, cudaStream_t st);
+cudaError_t launch_merge_blocks(const DevSchema& S, const DevTables& T, const bh_record* recs, const uint32_t* hist,
+                                uint32_t n_blocks, uint64_t stride, const unsigned long long* counts, cudaStream_t st);
 cudaError_t launch_close_window(const DevTables& T, uint64_t window_id, cudaStream_t st);
+cudaError_t launch_reset_tables(const DevTables& T, cudaStream_t st);
 cudaError_t configure_kernels(const LaunchGeom& G);
 cudaError_t launch_init_tables(const DevTables& T, cudaStream_t st);
 

@@ -43,7 +43,7 @@ class Aggregator:
                  hist_buckets: int = 64, hist_e0: int = DEFAULT_HIST_E0, hash_seed: int = 0xBE401DE5,
                  device: int = 0, slab_bytes: int = 0, slab_events: int = 0, n_slabs: int = 0,
                  enum_drop: bool = True, message_bytes_hint: int = 0, generic_kernels: bool = False,
-                 max_batch_latency_ms: int = 0, flags: int = 0):
+                 max_batch_latency_ms: int = 0, flags: int = 0, part_region_tuples: int = 0, _handle=None):
         schema = schema or telemetry_progress()
         if mode == L.MODE_WINDOWED:
             schema = schema.with_roles(key=key)
@@ -65,6 +65,7 @@ class Aggregator:
         cfg.message_bytes_hint = message_bytes_hint
         cfg.flags = (L.F_GENERIC_KERNELS if generic_kernels else 0) | flags
         cfg.max_batch_latency_ms = max_batch_latency_ms
+        cfg.part_region_tuples = part_region_tuples
         self._commit_cb = None
         fill_config(cfg, schema)
         if not enum_drop:
@@ -74,11 +75,27 @@ class Aggregator:
         self.ops = ops | L.OP_COUNT if mode == L.MODE_WINDOWED else L.OP_COUNT
         self.hist_buckets = hist_buckets or 64
         self.device = device
-        self._ctx = C.c_void_p()
-        L.check(L.lib.bh_create(C.byref(cfg), C.byref(self._ctx)))
+        self._owns = _handle is None            # a context that belongs to a bh_group is destroyed by the group
+        if _handle is not None:
+            self._ctx = C.c_void_p(_handle)
+        elif _handle is None and not getattr(self, "_config_only", False):
+            self._ctx = C.c_void_p()
+            L.check(L.lib.bh_create(C.byref(cfg), C.byref(self._ctx)))
 
     # ---- lifecycle ----
+    @classmethod
+    def config(cls, *args, **kw) -> "L.BhConfig":
+        """the bh_config these arguments describe, without creating a context (for bh_create_group)"""
+        self = cls.__new__(cls)
+        self._config_only = True
+        self._ctx = C.c_void_p()
+        cls.__init__(self, *args, **kw)
+        return self.cfg
+
     def close(self) -> None:
+        if self._ctx and not getattr(self, "_owns", True):
+            self._ctx = C.c_void_p()
+            return
         if self._ctx:
             L.lib.bh_destroy(self._ctx)       # stops the completion thread before anything is freed
             self._ctx = C.c_void_p()
@@ -164,6 +181,13 @@ class Aggregator:
         built into the library (at most BH_STATIC_EXPORT_MAX_OWNERS owners; calls on one GPU must not overlap)"""
         self._ck(L.lib.bh_export_window_static(self._ctx, window_id, n_owners, _ptr(d_records), _ptr(d_hist), cap,
                                                owner_stride, _ptr(d_owner_counts), stream or None))
+
+    def close_window_device(self, window_id: int, stream: int = 0) -> None:
+        self._ck(L.lib.bh_close_window_device(self._ctx, window_id, stream or None))
+
+    def drain_device(self, stream: int = 0) -> None:
+        """partitioned aggregation: fold the logged tuples into the tables now (reads do it by themselves)"""
+        self._ck(L.lib.bh_drain_device(self._ctx, stream or None))
 
     def reset_device(self, stream: int = 0) -> None:
         self._ck(L.lib.bh_reset_device(self._ctx, stream or None))

@@ -49,6 +49,8 @@ def parse_args():
     ap.add_argument("--events", type=int, default=EVENTS_PER_GPU, help="events per GPU per step")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-extra", action="store_true", help="skip the c3 / c4 / c5 legs (BASELINE.json configs 3-5)")
+    ap.add_argument("--c3-events", type=int, default=1_000_000_000, help="events streamed by the c3 leg (per GPU in the c4 leg)")
     return ap.parse_args()
 
 
@@ -60,11 +62,11 @@ def peaks():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
-def ncu_traffic():
+def ncu_traffic(key="k_process_raw_dram_bytes_per_launch"):
     p = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(p):
         with open(p) as f:
-            return json.load(f).get("k_process_raw_dram_bytes_per_launch")
+            return json.load(f).get(key)
     return None
 
 
@@ -225,6 +227,50 @@ def run_reference(args):
     }))
 
 
+def oracle_exchange_check(local, owned, exch, world, rank, device, stream, n=1_000_000):
+    """The exchange the timed loop used, against the CPU oracle: every rank feeds the first n events of its share,
+    one window close moves the rows to their owners, and each rank compares the rows it now owns with the oracle's
+    table of ALL ranks' events reduced to its keys.  Outside every timed region."""
+    import numpy as np
+    import torch
+    import beholder_b200 as bh
+    from beholder_b200 import _lib as L
+    from beholder_b200.dist import owner_of
+    from beholder_b200.synth import generate_device
+    from oracle import oracle as O
+    torch.cuda.synchronize()
+    local.reset_device(stream=stream); owned.reset_device(stream=stream)
+    spec, first = spec_for(rank, EVENTS_PER_GPU)
+    p, o, t, _ = generate_device(spec, first, n, device=device)
+    local.process_device(p, o, t, n, stream=stream)
+    exch.close_all_windows(reset_local=True)
+    torch.cuda.synchronize()
+    owned.sync()
+    got = owned.snapshot_all()
+    schema = bh.telemetry_progress().with_roles(key=("mediaId", "status"))
+    ops = L.OP_COUNT | L.OP_SUM | L.OP_MIN | L.OP_MAX
+    a = O.Agg(schema, ops, WINDOW_MS, 0xBE401DE5)
+    for r in range(world):
+        sp, fr = spec_for(r, EVENTS_PER_GPU)
+        p, o, t, _ = generate_device(sp, fr, n, device=device)
+        part = O.Agg.run_threads(schema, ops, WINDOW_MS, 0xBE401DE5, p.cpu().numpy(), o.cpu().numpy().view(np.uint32),
+                                 t.cpu().numpy().view(np.uint64), min(8, os.cpu_count() or 1))
+        a.merge(part)
+    want = a.snapshot()
+    want = want[owner_of(want["key_hash"], world) == rank]
+    got = got[np.lexsort((got["key_hash"], got["window_id"]))]
+    want = want[np.lexsort((want["key_hash"], want["window_id"]))]
+    assert len(got) == len(want) and len(want) > 0, (len(got), len(want))
+    for f in ("key_hash", "window_id", "count"):
+        assert np.array_equal(got[f], want[f]), f
+    for f in ("min", "max"):
+        assert np.array_equal(got[f].view(np.uint64), want[f].view(np.uint64)), f
+    assert np.allclose(got["sum"], want["sum"], rtol=1e-6, atol=0)
+    local.reset_device(stream=stream); owned.reset_device(stream=stream)
+    torch.cuda.synchronize()
+    return "oracle-equal"
+
+
 def workload_config(n_gpus: int):
     return {"workload": f"C2: per GPU {EVENTS_PER_GPU} synthetic api.TelemetryProgress events x {PAYLOAD_BYTES} B, "
                         f"{N_KEYS} distinct (mediaId,status) keys, {WINDOW_MS // 1000} s tumbling windows, count/sum/min/max, "
@@ -234,6 +280,217 @@ def workload_config(n_gpus: int):
             "l2_policy": "inputs (7.6 GB per GPU per step) are larger than L2; no explicit flush",
             "parallelism": f"events sharded over {n_gpus} GPU(s); key-hash owner merge per step when N>1 "
                            f"(export kernel stores into the owners' buffers over NVLink, or NCCL all-to-all: see 'exchange')"}
+
+
+# ------------------------------------------------------------------------------------------
+# BASELINE.json configs 3, 4, 5 beside the headline: one dictionary each in the JSON line
+# ------------------------------------------------------------------------------------------
+MANY_RATE = 5000            # events per ms of stream time: 1 B events = 200 s = 20 windows of 10 s
+MANY_SLAB = 12_500_000
+MANY_JITTER = 2000
+
+
+def many_key_pass(local, slabs, first_index, stream, on_close):
+    """one pass over pre-generated slabs of a many-key stream, windows closed behind the watermark"""
+    import beholder_b200 as bh
+    t0 = 1_700_000_000_000
+    ws = bh.WindowStream(local, WINDOW_MS, on_close)
+    g = first_index
+    for p, o, t, n, _ in slabs:
+        ws.process_device(p, o, t, n, first_ts_ms=t0 + g // MANY_RATE - MANY_JITTER,
+                          watermark_ms=t0 + (g + n) // MANY_RATE - MANY_JITTER, stream=stream)
+        g += n
+    ws.finish(t0 + g // MANY_RATE + MANY_JITTER, stream)
+    return ws.closed
+
+
+def many_key_slabs(keys, events, rank, device, f64):
+    import torch
+    from beholder_b200.synth import SynthSpec, generate_device
+    spec = SynthSpec(n_keys=keys, rate_per_ms=MANY_RATE, jitter_ms=MANY_JITTER, payload_bytes=PAYLOAD_BYTES, value_f64=f64,
+                     value_exp_lo=-12, value_exp_span=24)
+    slabs, g = [], 0
+    first = rank * events           # ranks take consecutive stretches of the event index space ...
+    spec.t0_ms -= first // MANY_RATE  # ... that cover the same stream time (round-robin delivery)
+    while g < events:
+        n = min(MANY_SLAB, events - g)
+        p, o, t, total = generate_device(spec, first + g, n, device=device)
+        slabs.append((p[: (total + 15) // 16 * 16 + 16].clone(), o, t, n, total))
+        g += n
+    torch.cuda.synchronize()
+    return slabs, first
+
+
+def c3_leg(args, device, stream, peak):
+    """configs[2]: 1 GPU, 1 B events streamed once, 1 M distinct keys, 64-bucket log2 histograms, f64 values.  The
+    whole stream is resident in HBM (76 GB of the 180); tables live in a ring of 4 windows, every window is
+    exported to a device buffer (rows + histograms) and recycled as the watermark passes it."""
+    import torch
+    import beholder_b200 as bh
+    from beholder_b200 import _lib as L
+    events, keys, cap = args.c3_events, 1_000_000, 1 << 21
+    ops = L.OP_COUNT | L.OP_SUM | L.OP_MIN | L.OP_MAX | L.OP_HIST
+    slabs, first = many_key_slabs(keys, events, 0, device, True)
+    g = bh.Aggregator(bh.telemetry_progress(L.K_DOUBLE), mode=L.MODE_WINDOWED, ops=ops, window_ms=WINDOW_MS,
+                      table_capacity=cap, window_ring=4, device=device)
+    rows = torch.zeros(cap + 2, 6, dtype=torch.int64, device="cuda")
+    hist = torch.zeros(cap + 2, 64, dtype=torch.int32, device="cuda")
+    cnt = torch.zeros(1, dtype=torch.int64, device="cuda")
+    exported = torch.zeros(1, dtype=torch.int64, device="cuda")
+
+    def on_close(w, st):
+        g.export_window_device(w, 1, rows, hist, cap + 2, cnt, stream=st)
+        exported.add_(cnt)
+        g.close_window_device(w, stream=st)
+
+    # warm-up (timing rule: never time a kernel's first launches): the first slab three times, windows closed
+    for _ in range(3):
+        many_key_pass(g, slabs[:1], first, stream, on_close)
+    g.reset_device(stream=stream); exported.zero_()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    closed = many_key_pass(g, slabs, first, stream, on_close)
+    e1.record(); torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1)
+    k = g.counters()
+    assert k["events_ok"] == events and k["dropped_table_full"] == 0 and k["dropped_window"] == 0, k
+    assert not g.list_windows()
+    nbytes = sum(total + 12 * n for *_, n, total in slabs)
+    out = {"workload": f"C3: {events} events x {PAYLOAD_BYTES} B streamed once, {keys} distinct keys, {WINDOW_MS // 1000} s windows, "
+                       f"count/sum/min/max + 64-bucket log2 histograms, f64 values; window ring 4, each window exported (rows + "
+                       f"histograms) to a device buffer and recycled behind the watermark",
+           "value": events / (ms * 1e-3), "unit": UNIT, "ms": ms, "events": events, "keys": keys, "windows_closed": closed,
+           "rows_exported": int(exported.item()), "smem_miss_frac": k["smem_spills"] / events,
+           "roofline": {"bound": "hbm", "kernels": "bh::k_process_raw + bh::k_part_drain + export/close", "achieved": nbytes / (ms * 1e-3) / 1e9,
+                        "peak": peak, "unit": "GB/s", "frac": nbytes / (ms * 1e-3) / 1e9 / peak, "algorithmic_bytes_per_event": BYTES_PER_EVENT,
+                        "traffic_bytes_per_event": ncu_traffic("c3_dram_bytes_per_event"),
+                        "note": "whole pass (decode + log + fold + export + close) against the 76 B/event the input costs; table "
+                                "and log traffic are extra (traffic_bytes_per_event, from ncu)"}}
+    g.close()
+    del slabs
+    torch.cuda.empty_cache()
+    return out
+
+
+def c4_leg(args, world, rank, device, stream, peak):
+    """configs[3]: N GPUs, events spread by arrival, 10 M distinct keys seen by every GPU, per-window partial
+    aggregates moved to their key-hash owners over NVLink and merged there (the library's own exchange)."""
+    import torch
+    import torch.distributed as dist
+    import beholder_b200 as bh
+    from beholder_b200 import _lib as L
+    from beholder_b200.dist import MemberExchange
+    events, keys = args.c3_events, 10_000_000
+    ops = L.OP_COUNT | L.OP_SUM | L.OP_MIN | L.OP_MAX
+    slabs, first = many_key_slabs(keys, events, rank, device, False)
+    local = bh.Aggregator(mode=L.MODE_WINDOWED, ops=ops, window_ms=WINDOW_MS, table_capacity=1 << 24, window_ring=4, device=device)
+    own_cap = 1 << max(16, (int(keys * 1.6 / world) - 1).bit_length())
+    owned = bh.Aggregator(mode=L.MODE_WINDOWED, ops=ops, window_ms=WINDOW_MS, table_capacity=own_cap, window_ring=32, device=device,
+                          flags=L.F_NO_PARTITION)
+    stride = int(keys / world * 1.15) + 4096
+    ex = MemberExchange(local, owned, world, rank, owner_stride=stride, device=device)
+    t_close = []
+
+    def on_close(w, st):
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(); ex.close_window(w, st); b.record()
+        t_close.append((a, b))
+
+    for _ in range(3):                                # warm-up: first slab, windows closed through the exchange
+        many_key_pass(local, slabs[:1], first, stream, on_close)
+    torch.cuda.synchronize(); dist.barrier()
+    local.reset_device(stream=stream); owned.reset_device(stream=stream); t_close.clear()
+    dist.barrier(); torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    closed = many_key_pass(local, slabs, first, stream, on_close)
+    e1.record(); torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1)
+    sent = ex.check_no_overflow()                     # rows of the last close per owner; raises if any block was cut
+    k = local.counters()
+    assert k["events_ok"] == events and k["dropped_table_full"] == 0 and k["dropped_window"] == 0, k
+    owned.sync()
+    ko = owned.counters()
+    assert ko["dropped_table_full"] == 0 and ko["dropped_window"] == 0, ko
+    # every event counted exactly once across the owners' tables
+    total_owned = 0
+    for w in owned.list_windows():
+        total_owned += int(owned.snapshot(w, cap=own_cap + 2)["count"].sum())
+    close_ms = sum(a.elapsed_time(b) for a, b in t_close)
+    t = torch.tensor([ms, close_ms, float(total_owned), float(sum(sent))], dtype=torch.float64, device="cuda")
+    tmax = t.clone(); dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+    tsum = t.clone(); dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
+    ms, close_ms = tmax[0].item(), tmax[1].item()
+    assert int(tsum[2].item()) == world * events, (int(tsum[2].item()), world * events)
+    rows_per_close = tsum[3].item() / world
+    nvlink_bytes = rows_per_close * 48 * (world - 1) / world
+    out = {"workload": f"C4: {world} GPUs x {events} events x {PAYLOAD_BYTES} B, {keys} distinct keys seen by every GPU, {WINDOW_MS // 1000} s "
+                       f"windows, count/sum/min/max; per-window partial rows stored into their key-hash owners' buffers over NVLink and "
+                       f"merged (bh_member_close_window), window ring 4",
+           "value": world * events / (ms * 1e-3), "unit": UNIT, "ms": ms, "events_per_gpu": events, "keys": keys,
+           "windows_closed": closed, "close_ms_total": close_ms, "close_ms_per_window": close_ms / max(1, closed),
+           "close_share_of_pass": close_ms / ms, "rows_sent_per_gpu_per_close": rows_per_close,
+           "nvlink_bytes_per_gpu_per_close": nvlink_bytes,
+           "nvlink_gbs_during_close": nvlink_bytes / (close_ms / max(1, closed) * 1e-3) / 1e9 if close_ms else None,
+           "exchange_check": "every event counted once in the owners' tables (sum of counts == N x events)",
+           "per_gpu_algorithmic_gbs": events * BYTES_PER_EVENT / (ms * 1e-3) / 1e9, "frac_of_hbm_peak": events * BYTES_PER_EVENT / (ms * 1e-3) / 1e9 / peak}
+    ex.close(); local.close(); owned.close()
+    del slabs
+    torch.cuda.empty_cache()
+    return out
+
+
+def c5_leg(device, stream, peak, pcie_peak):
+    """configs[4] on this GPU: payload 64 B .. 4 KB, HBM-resident and end to end.  Bytes: `read_bytes` counts what
+    the kernel has to touch -- all of a message while batches are staged through shared memory (<= 288 B), the
+    fields it parses plus the headers it skips once messages are read from global memory (the pad is skipped)."""
+    import numpy as np
+    import torch
+    import beholder_b200 as bh
+    from beholder_b200 import _lib as L
+    from beholder_b200.synth import SynthSpec, generate_device
+    ops = L.OP_COUNT | L.OP_SUM | L.OP_MIN | L.OP_MAX
+    out = []
+    for payload in (64, 128, 256, 512, 1024, 2048, 4096):
+        n = max(500_000, min(12_500_000, (800 << 20) // payload))
+        spec = SynthSpec(n_keys=N_KEYS, rate_per_ms=500, payload_bytes=payload)
+        p, o, t, total = generate_device(spec, 0, n, device=device)
+        mk = lambda: bh.Aggregator(mode=L.MODE_WINDOWED, ops=ops, window_ms=WINDOW_MS, table_capacity=2048, window_ring=32,  # noqa: E731
+                                   device=device, message_bytes_hint=payload, slab_bytes=64 << 20, slab_events=1 << 20, n_slabs=4)
+        g = mk()
+        for _ in range(3):
+            g.process_device(p, o, t, n, stream=stream)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(5):
+            g.process_device(p, o, t, n, stream=stream)
+        e1.record(); torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / 5
+        g.close()
+        staged = payload <= 288
+        touched = (total if staged else n * 96) + 12 * n     # global-memory reader: ~64 B of fields + 32 B sectors of the skipped pad's header
+        pb = bh.PinnedBuffer(p.numel()); ob = bh.PinnedBuffer((n + 1) * 4); tb = bh.PinnedBuffer(n * 8)
+        hp, ho, ht = pb.view(np.uint8), ob.view(np.uint32), tb.view(np.uint64)
+        torch.from_numpy(hp).copy_(p); torch.from_numpy(ho.view(np.int32)).copy_(o); torch.from_numpy(ht.view(np.int64)).copy_(t)
+        torch.cuda.synchronize()
+        g = mk()
+        g.push_batch(hp, ho, ht, pinned=True); g.flush()
+        t0 = time.perf_counter()
+        for _ in range(2):
+            g.push_batch(hp, ho, ht, pinned=True)
+        g.flush()
+        dt = (time.perf_counter() - t0) / 2
+        g.close(); pb.free(); ob.free(); tb.free()
+        wire = total + 12 * n
+        hbm_frac, pcie_frac = touched / (ms * 1e-3) / 1e9 / peak, wire / dt / 1e9 / pcie_peak
+        out.append({"payload_bytes": payload, "events": n, "hbm_events_per_s": n / (ms * 1e-3), "hbm_read_gbs": touched / (ms * 1e-3) / 1e9,
+                    "hbm_frac": hbm_frac, "e2e_events_per_s": n / dt, "e2e_pcie_gbs": wire / dt / 1e9, "e2e_pcie_frac": pcie_frac,
+                    "regime": "ingest-bound end to end (PCIe); HBM-resident: " +
+                              ("instruction issue (decode)" if staged else "latency of per-message global reads (pad skipped, not read)")})
+        del p, o, t
+    torch.cuda.empty_cache()
+    return out
 
 
 # ------------------------------------------------------------------------------------------
@@ -281,20 +538,18 @@ def main():
     if world > 1:
         owned = mk()
         stride = 2 * (N_KEYS * 40) // world
-        exchange = os.environ.get("BEHOLDER_EXCHANGE", "peer")
-        if exchange == "peer":
-            # export kernel stores straight into the owners' buffers over NVLink (torch symmetric memory);
-            # every rank must take the same branch, so a failure anywhere sends all of them to NCCL
-            okay = torch.ones(1, device="cuda")
+        # "member" (default): the library's own exchange -- receive areas shared as CUDA IPC handles, the export
+        # kernel stores rows straight into the owners' buffers over NVLink, a flag barrier in peer memory, merge;
+        # torch.distributed only carried the handles.  "nccl": export -> all_to_all_single -> merge.  A failure to
+        # map the peers' memory raises on every rank together (MemberExchange), so all of them fall back together.
+        exchange = os.environ.get("BEHOLDER_EXCHANGE", "member")
+        if exchange == "member":
             try:
-                from beholder_b200.dist import PeerWindowExchange
-                exch = PeerWindowExchange(local, owned, world, rank, owner_stride=stride, device=local_rank)
-            except Exception as e:      # noqa: BLE001 - symmetric memory unavailable on this box
-                print(f"[bench] rank {rank}: peer exchange unavailable ({e}); using NCCL all-to-all", file=sys.stderr)
-                okay.zero_()
-            dist.all_reduce(okay, op=dist.ReduceOp.MIN)
-            if okay.item() == 0:
-                exch, exchange = None, "nccl"
+                from beholder_b200.dist import MemberExchange
+                exch = MemberExchange(local, owned, world, rank, owner_stride=stride, device=local_rank)
+            except Exception as e:      # noqa: BLE001 - CUDA IPC between the ranks unavailable on this box
+                print(f"[bench] rank {rank}: member exchange unavailable ({e}); using NCCL all-to-all", file=sys.stderr)
+                exch = None
         if exch is None:
             exchange = "nccl"
             exch = WindowExchange(local, owned, world, rank, owner_stride=stride, device=local_rank)
@@ -338,6 +593,7 @@ def main():
     value = world * events * args.steps / (total_ms * 1e-3)
 
     # correctness guard on what was just timed: every event counted exactly once
+    exchange_check = None
     if exch is None:
         k = local.counters()
         done = max(args.warmup, 3) + args.steps
@@ -346,6 +602,16 @@ def main():
         exch.check_no_overflow()
         k = local.counters()
         assert k["dropped_table_full"] == 0 and k["dropped_window"] == 0, k
+        done = max(args.warmup, 3) + args.steps
+        if exchange == "member":       # (the NCCL exchange resets the local counters with the tables)
+            assert k["events_ok"] == events * done, (k, events * done)
+        # every event of every rank and step sits in exactly one owner's table
+        owned.sync()
+        mine = sum(int(owned.snapshot(w, cap=4096)["count"].sum()) for w in owned.list_windows())
+        tot = torch.tensor([float(mine)], dtype=torch.float64, device="cuda")
+        dist.all_reduce(tot, op=dist.ReduceOp.SUM)
+        assert int(tot.item()) == world * events * done, (int(tot.item()), world * events * done)
+        exchange_check = oracle_exchange_check(local, owned, exch, world, rank, local_rank, stream)
 
     # ---- the reference's literal semantics on the same slabs (index.js:136-138: one counter per status,
     # no key hash, no windows, no timestamps): reported beside the headline, not instead of it ----
@@ -425,12 +691,25 @@ def main():
         del dst
         ing = mk()
         h2d = sum(total + (n + 1) * 4 + n * 8 for *_, n, total in pins)
+        ing_owned = ing_ex = None
+        if world > 1 and exchange == "member":
+            from beholder_b200.dist import MemberExchange
+            ing_owned = mk()
+            ing_ex = MemberExchange(ing, ing_owned, world, rank, owner_stride=stride, device=local_rank)
 
         def e2e_step():
             for _, _, _, hp, ho, ht, n, _ in pins:
                 ing.push_batch(hp, ho, ht, pinned=True)
             ing.flush()
             rows = 0
+            if ing_ex is not None:
+                # N > 1: the step's result is the OWNERS' tables: window close over NVLink, then each rank reads
+                # the rows it owns back to the host
+                ing_ex.close_window(None)
+                for w in ing_owned.list_windows():
+                    rows += len(ing_owned.snapshot(w, cap=4096))
+                ing_owned.reset_device()
+                return rows
             for w in ing.list_windows():
                 rows += len(ing.snapshot(w, cap=4096))
             return rows
@@ -453,7 +732,8 @@ def main():
         e2e = {"value": world * events * e2e_steps / dt, "unit": UNIT, "h2d_bytes_per_step": h2d,
                "d2h_bytes_per_step": rows * 48 + 8 * 40, "steps": e2e_steps,
                "path": "bh_push_batch_pinned -> (pinned host -> HBM in 64 MiB ring slabs on 2 copy streams) -> "
-                       "k_process_raw -> bh_flush -> bh_snapshot of every window",
+                       "k_process_raw -> bh_flush -> " + ("window close to the key owners over NVLink -> bh_snapshot of the owned windows"
+                                                          if ing_ex is not None else "bh_snapshot of every window"),
                "pcie_gbs": world * h2d * e2e_steps / dt / 1e9,
                "pcie_peak_gbs_per_gpu": pcie_peak}
         if pcie_concurrent is None:
@@ -465,6 +745,31 @@ def main():
                         "pcie_frac_of_n_x_solo": e2e["pcie_gbs"] / (world * pcie_peak),
                         "bound": "PCIe H2D ingest with all N GPUs copying at once (pcie_concurrent_peak_gbs = all bytes / time "
                                  "until the slowest GPU is done, measured; pcie_peak_gbs_per_gpu is one GPU copying alone)"})
+        if ing_ex is not None:
+            ing_ex.close(); ing_owned.close()
+        if world == 1:
+            # the drop-in ingest paths: what a Node Buffer goes through.  (a) bh_push_batch from ordinary (pageable)
+            # host memory: the library copies into its pinned ring first; (b) bh_push, one call per message, as
+            # addon/beholder_napi.c does for each rmsg.message.content (index.js:129) -- driven from C so that no
+            # Python call overhead is measured (bh_debug_push_each: a loop over bh_push).
+            hp0, ho0, ht0, n0, total0 = pins[0][3], pins[0][4], pins[0][5], pins[0][6], pins[0][7]
+            pg = (np.array(hp0, copy=True), np.array(ho0, copy=True), np.array(ht0, copy=True))     # pageable copies
+            b0 = total0 + (n0 + 1) * 4 + n0 * 8
+            variants = {}
+            for name, fn in (("pageable_batch", lambda: ing.push_batch(*pg)),
+                             ("per_message_push", lambda: L.check(L.lib.bh_debug_push_each(ing._ctx, pg[0].ctypes.data, pg[1].ctypes.data,
+                                                                                          pg[2].ctypes.data, n0), ing._ctx))):
+                fn(); ing.flush()
+                t0 = time.perf_counter()
+                reps = 3
+                for _ in range(reps):
+                    fn()
+                ing.flush()
+                d = (time.perf_counter() - t0) / reps
+                variants[name] = {"value": n0 / d, "unit": UNIT, "events": n0, "pcie_gbs": b0 / d / 1e9, "pcie_frac": b0 / d / 1e9 / pcie_peak}
+            variants["pageable_batch"]["path"] = "bh_push_batch (pageable host slab -> memcpy into the pinned ring on copy threads -> H2D -> kernel)"
+            variants["per_message_push"]["path"] = "bh_push per message from C (what the N-API shim does per rmsg) -> pinned ring -> H2D -> kernel"
+            e2e["variants"] = variants
         ing.close()
         for pb, ob, tb, *_ in pins:
             pb.free(); ob.free(); tb.free()
@@ -486,6 +791,7 @@ def main():
                          "avg_launch_ms": per_launch_s * 1e3},
             "gpu_launches": launches_per_step * args.steps,
             "exchange": (exchange if world > 1 else None),
+            "exchange_check": (exchange_check if world > 1 else None),
             "clocks": clocks,
         }
         if e2e:
@@ -495,8 +801,30 @@ def main():
             line["reference_mode"] = ref_mode
         if world == 1 and not args.no_cpu:
             line["cpu_baseline"] = cpu_baseline_block(True)
+    # ---- BASELINE.json configs 3, 4, 5 (extra keys of the same line; a failure is reported, not fatal) ----
+    extra = {}
+    if not args.no_extra:
+        local.close(); local = None
+        if exch is not None and hasattr(exch, "close"):
+            exch.close()
+        del slabs
+        torch.cuda.empty_cache()
+        peak_gbs = peaks()[0]
+        legs = [("c3", lambda: c3_leg(args, local_rank, stream, peak_gbs)),
+                ("c5", lambda: c5_leg(local_rank, stream, peak_gbs, e2e["pcie_peak_gbs_per_gpu"] if e2e else 55.0))] if world == 1 else \
+               [("c4", lambda: c4_leg(args, world, rank, local_rank, stream, peak_gbs))]
+        for name, fn in legs:
+            try:
+                extra[name] = fn()
+            except Exception as e:      # noqa: BLE001
+                if world > 1:
+                    raise               # a rank that skipped a collective would hang the others
+                extra[name] = {"error": f"{type(e).__name__}: {e}"}
+    if rank == 0:
+        line.update(extra)
         print(json.dumps(line))
-    local.close()
+    if local is not None:
+        local.close()
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()

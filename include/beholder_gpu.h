@@ -237,12 +237,58 @@ int bh_export_window_peers(bh_ctx* ctx, uint64_t window_id, uint32_t n_owners, c
 int bh_export_window_static(bh_ctx* ctx, uint64_t window_id, uint32_t n_owners, bh_record* d_records,
                             uint32_t* d_hist, uint64_t cap, uint64_t owner_stride,
                             uint64_t* d_owner_counts, void* stream);
+/* bh_close_window on the caller's stream (after the window has been exported); BH_ALL_WINDOWS closes every open one */
+int bh_close_window_device(bh_ctx* ctx, uint64_t window_id, void* stream);
+/* partitioned aggregation (BH_F_PARTITIONED): fold everything logged so far into the tables now.  Reads do this
+ * by themselves; a caller that times or overlaps work can choose the moment.  No-op otherwise. */
+int bh_drain_device(bh_ctx* ctx, void* stream);
 /* drop every window and zero the drop counters (the counters of index.js:32 "reset on restart") */
 int bh_reset_device(bh_ctx* ctx, void* stream);
 /* merge partial rows (from other GPUs) into this context's tables */
 int bh_merge_records_device(bh_ctx* ctx, const bh_record* d_records, const uint32_t* d_hist,
                             uint64_t n, void* stream);
 int bh_sync(bh_ctx* ctx);
+/* like bh_merge_records_device for rows that arrived in n_blocks blocks of block_stride rows (one per sending GPU):
+ * block b holds min(d_block_counts[b], block_stride) valid rows; nothing beyond is read */
+int bh_merge_blocks_device(bh_ctx* ctx, const bh_record* d_records, const uint32_t* d_hist, uint32_t n_blocks,
+                           uint64_t block_stride, const uint64_t* d_block_counts, void* stream);
+/* the context's own stream (a cudaStream_t): what `stream = NULL` means in the entry points above.  To name CUDA's
+ * legacy default stream pass (void*)1 (cudaStreamLegacy), never NULL. */
+void* bh_stream(bh_ctx* ctx);
+/* make the context's own stream wait for everything queued on `stream` so far */
+int bh_stream_wait(bh_ctx* ctx, void* stream);
+
+/* ---- multi-GPU: key-hash sharded window close inside the library (SURVEY 8 b/e).  No counterpart in the
+ * reference, which is the single process of index.js:23-48; this is what lets that one process drive several
+ * GPUs.  Events are spread over the GPUs by arrival, `local` contexts aggregate what they see, a key's merged
+ * row lives in the `owned` context of GPU (key_hash >> (64 - log2 n)).  bh_group_close_window runs, on every GPU
+ * and asynchronously on its stream: export rows straight into the owners' receive buffers over NVLink ->
+ * cross-GPU flag barrier -> merge -> recycle the window.  owner_stride = rows one GPU can send one owner per
+ * close (exceeding it is reported by bh_group_sync as BH_ERR_TOO_LARGE, never silent). ---- */
+typedef struct bh_group bh_group;
+typedef struct bh_member bh_member;
+int bh_create_group(const bh_config* local_cfg, const bh_config* owned_cfg, const int* devices, uint32_t n,
+                    uint64_t owner_stride, bh_group** out);          /* the configs' `device` fields are ignored */
+void bh_group_destroy(bh_group* g);
+uint32_t bh_group_size(bh_group* g);
+bh_ctx* bh_group_local(bh_group* g, uint32_t rank);   /* push / process this GPU's share of the events here */
+bh_ctx* bh_group_owned(bh_group* g, uint32_t rank);   /* snapshot the keys this GPU owns here */
+bh_member* bh_group_member(bh_group* g, uint32_t rank);
+int bh_group_close_window(bh_group* g, uint64_t window_id);          /* BH_ALL_WINDOWS: every open window */
+int bh_group_sync(bh_group* g);                        /* waits for every GPU; reports cut rows */
+const char* bh_group_last_error(void);
+/* One member per process (one process per GPU, e.g. under torchrun): create, exchange the 64-byte handles of
+ * bh_member_ipc_handle between the ranks by any means, connect, then bh_member_close_window on every rank. */
+#define BH_IPC_HANDLE_BYTES 64
+int bh_member_create(bh_ctx* local, bh_ctx* owned, int device, uint32_t rank, uint32_t world, uint64_t owner_stride,
+                     uint32_t hist_buckets, bh_member** out);
+void bh_member_destroy(bh_member* m);
+int bh_member_ipc_handle(bh_member* m, void* out64);
+int bh_member_connect_ipc(bh_member* m, const void* handles /* world x 64 bytes, by rank */);
+int bh_member_connect_ptrs(bh_member* m, void* const* areas /* world device pointers (same process) */);
+void* bh_member_area(bh_member* m);
+int bh_member_close_window(bh_member* m, uint64_t window_id, void* stream);
+int bh_member_check(bh_member* m, uint64_t* owner_counts_out /* world values of the last close, may be NULL */);
 
 /* ---- synthetic event streams (bench/test input) ---- */
 typedef struct bh_synth_config {
