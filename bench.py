@@ -290,12 +290,13 @@ MANY_SLAB = 12_500_000
 MANY_JITTER = 2000
 
 
-def many_key_pass(local, slabs, first_index, stream, on_close):
-    """one pass over pre-generated slabs of a many-key stream, windows closed behind the watermark"""
+def many_key_pass(local, slabs, stream, on_close):
+    """one pass over pre-generated slabs of a many-key stream, windows closed behind the watermark (every rank's
+    slabs cover the same stream time: many_key_slabs shifts t0 by the rank's first event index)"""
     import beholder_b200 as bh
     t0 = 1_700_000_000_000
     ws = bh.WindowStream(local, WINDOW_MS, on_close)
-    g = first_index
+    g = 0
     for p, o, t, n, _ in slabs:
         ws.process_device(p, o, t, n, first_ts_ms=t0 + g // MANY_RATE - MANY_JITTER,
                           watermark_ms=t0 + (g + n) // MANY_RATE - MANY_JITTER, stream=stream)
@@ -345,12 +346,12 @@ def c3_leg(args, device, stream, peak):
 
     # warm-up (timing rule: never time a kernel's first launches): the first slab three times, windows closed
     for _ in range(3):
-        many_key_pass(g, slabs[:1], first, stream, on_close)
+        many_key_pass(g, slabs[:1], stream, on_close)
     g.reset_device(stream=stream); exported.zero_()
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
-    closed = many_key_pass(g, slabs, first, stream, on_close)
+    closed = many_key_pass(g, slabs, stream, on_close)
     e1.record(); torch.cuda.synchronize()
     ms = e0.elapsed_time(e1)
     k = g.counters()
@@ -398,13 +399,13 @@ def c4_leg(args, world, rank, device, stream, peak):
         t_close.append((a, b))
 
     for _ in range(3):                                # warm-up: first slab, windows closed through the exchange
-        many_key_pass(local, slabs[:1], first, stream, on_close)
+        many_key_pass(local, slabs[:1], stream, on_close)
     torch.cuda.synchronize(); dist.barrier()
     local.reset_device(stream=stream); owned.reset_device(stream=stream); t_close.clear()
     dist.barrier(); torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
-    closed = many_key_pass(local, slabs, first, stream, on_close)
+    closed = many_key_pass(local, slabs, stream, on_close)
     e1.record(); torch.cuda.synchronize()
     ms = e0.elapsed_time(e1)
     sent = ex.check_no_overflow()                     # rows of the last close per owner; raises if any block was cut
@@ -813,13 +814,33 @@ def main():
         legs = [("c3", lambda: c3_leg(args, local_rank, stream, peak_gbs)),
                 ("c5", lambda: c5_leg(local_rank, stream, peak_gbs, e2e["pcie_peak_gbs_per_gpu"] if e2e else 55.0))] if world == 1 else \
                [("c4", lambda: c4_leg(args, world, rank, local_rank, stream, peak_gbs))]
+        # The headline above must never be lost to an extra leg.  One GPU: an exception is recorded in the leg's
+        # place.  Several GPUs: a rank that failed would leave its peers waiting in a barrier for ever, so every
+        # rank arms a watchdog: past the deadline rank 0 prints the line with the leg marked as timed out and all
+        # ranks leave.
+        def give_up():
+            if rank == 0:
+                line.update(extra)
+                for name, _ in legs:
+                    line.setdefault(name, {"error": "leg did not finish within its deadline"})
+                print(json.dumps(line), flush=True)
+            os._exit(0)
+        dog = threading.Timer(float(os.environ.get("BEHOLDER_EXTRA_DEADLINE_S", "240")), give_up) if world > 1 else None
+        if dog:
+            dog.daemon = True; dog.start()
         for name, fn in legs:
             try:
                 extra[name] = fn()
             except Exception as e:      # noqa: BLE001
-                if world > 1:
-                    raise               # a rank that skipped a collective would hang the others
                 extra[name] = {"error": f"{type(e).__name__}: {e}"}
+                if world > 1:
+                    print(f"[bench] rank {rank}: {name} failed: {e}", file=sys.stderr, flush=True)
+                    if dog:
+                        dog.cancel()
+                    time.sleep(5)       # peers may be inside the leg's barriers: let the watchdogs of the others end the run
+                    give_up()
+        if dog:
+            dog.cancel()
     if rank == 0:
         line.update(extra)
         print(json.dumps(line))

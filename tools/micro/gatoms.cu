@@ -70,6 +70,39 @@ __global__ void __launch_bounds__(1024, 1) k_scatter(uint8_t* out, uint32_t P, u
   }
 }
 
+// scatter with ONE region per partition shared by all CTAs: cursor = a global atomic (with return) per tuple
+__global__ void __launch_bounds__(1024, 1) k_scatter_g(uint8_t* out, uint32_t P, uint32_t region_cap, uint64_t per_thread, uint64_t seed,
+                                                       unsigned int* gcur) {
+  uint64_t x = seed + blockIdx.x * 1024ull + threadIdx.x;
+  for (uint64_t i = 0; i < per_thread; i++) {
+    x = mix(x + i);
+    uint32_t p = (uint32_t)__umul64hi(x, P);
+    uint32_t pos = atomicAdd(&gcur[p], 1u);
+    if (pos < region_cap) *(uint4*)(out + ((uint64_t)p * region_cap + pos) * 16) = make_uint4((uint32_t)x, (uint32_t)(x >> 32), (uint32_t)i, p);
+  }
+}
+void run_scatter_g(uint32_t P) {
+  uint64_t per = 96;
+  uint32_t region_cap = (uint32_t)(148ull * 1024 * per / P * 2 + 64);
+  uint8_t* out; size_t bytes = (size_t)P * region_cap * 16;
+  unsigned int* gcur;
+  cudaMalloc(&out, bytes); cudaMalloc(&gcur, P * 4);
+  cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
+  cudaMemset(gcur, 0, P * 4);
+  k_scatter_g<<<148, 1024>>>(out, P, region_cap, per, 1, gcur);
+  float tot = 0;
+  for (int r = 0; r < 4; r++) {
+    cudaMemset(gcur, 0, P * 4);
+    cudaEventRecord(e0);
+    k_scatter_g<<<148, 1024>>>(out, P, region_cap, per, 5 + r, gcur);
+    cudaEventRecord(e1); cudaEventSynchronize(e1);
+    float ms; cudaEventElapsedTime(&ms, e0, e1); tot += ms;
+  }
+  double ops = 4.0 * 148 * 1024 * per;
+  printf("scatter 16-byte tuples, GLOBAL cursors, P=%5u (buffer %5.0f MB)   %7.2f Gtuple/s  err=%s\n", P, bytes / 1048576.0, ops / tot / 1e6, cudaGetErrorString(cudaGetLastError()));
+  cudaFree(out); cudaFree(gcur);
+}
+
 template <int MODE> void run(const char* name, uint64_t bytes) {
   uint64_t nrec = MODE == 0 ? bytes / 8 : bytes / 64;
   if (MODE == 3) nrec = bytes / 40;
@@ -106,8 +139,12 @@ template <int TB> void run_scatter(uint32_t P) {
   cudaFree(out);
 }
 
-int main() {
+int main(int argc, char** argv) {
   const uint64_t MB = 1048576;
+  if (argc > 1) {
+    for (uint32_t P : {256u, 1024u, 4096u, 16384u, 65536u}) { run_scatter_g(P); if (P <= 4096) run_scatter<16>(P); }
+    return 0;
+  }
   for (uint64_t f : {8 * MB, 32 * MB, 64 * MB, 128 * MB, 512 * MB, 2048 * MB}) {
     run<0>("u64 atomicAdd, random word", f);
     run<1>("64 B record: 4 atomics", f);
