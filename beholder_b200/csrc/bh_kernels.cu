@@ -860,11 +860,93 @@ __device__ __noinline__ bool decode_slow(const DevSchema& S, const SmemRd r, uin
   return decode_fast(S, r, len, P) || decode_event(S, r, len, P);
 }
 
+// ---- block tier -----------------------------------------------------------------------------------
+// A message that starts on a 4-byte boundary of the warp buffer and lies inside one 64-byte block of it is
+// CONTIGUOUS in shared memory (the skew only moves whole blocks), so its bytes are at base + i: no skew
+// arithmetic per access, aligned 32-bit loads, and the key bytes (at offset 2, after the one-byte tag and length)
+// come out of consecutive words with a constant 16-bit funnel shift.  Fixed-size 64-byte events on a 64-byte grid
+// (BASELINE.json config 2) are exactly that.  Accepted here: [string key or role-less string][one unknown
+// length-delimited field with a one-byte length]?[status][value][one role-less string or unknown
+// length-delimited field up to the end]? -- one-byte tags, lengths and varints, a 32-bit integer value, the key
+// made of that string and, optionally, the status.  That is a subset of what decode_canon accepts, with the same
+// field values by construction; anything else returns false with nothing decided and takes the tiers below.
+template <class SC>
+__device__ __forceinline__ bool decode_block(const SC& S, const SmemRd& r, uint32_t len, uint64_t& kh, uint32_t& status, uint32_t& uval) {
+  if (S.fast_value_f64 || S.tag_status > 0x7Fu || S.tag_value > 0x7Fu || S.identity_key) return false;
+  const bool key_is_string = S.tag_key0 <= 0x7Fu;
+  if (key_is_string ? !(S.n_parts == 1 || (S.n_parts == 2 && S.fast_status_part == 2)) : !S.status_part) return false;
+  const uint32_t x0 = r.off;
+  if ((x0 & 3u) || (x0 & 63u) + len > 64u || len < 6u) return false;
+  const uint32_t m = skew(x0);                               // bytes of the message: m + i
+  auto rd4 = [&](uint32_t pos) {                              // 4 bytes at any offset: two aligned words, one funnel shift
+    const uint32_t a = m + (pos & ~3u);
+    return __funnelshift_r(lds32(a), lds32(a + 4), (pos & 3u) * 8u);
+  };
+  const uint32_t w0 = lds32(m);
+  const uint32_t t0 = w0 & 0xFFu, klen = (w0 >> 8) & 0xFFu;
+  bool ok = key_is_string ? t0 == S.tag_key0 : (t0 < 0x80u && ((S.skip_str_mask >> (t0 >> 3)) & 1u));
+  ok = ok && klen < 0x80u;
+  uint32_t d = 2u + klen;
+  ok = ok && d + 4u <= len;
+  if (!ok) return false;
+  uint32_t x = rd4(d);
+  {
+    const uint32_t t = x & 0xFFu;                            // one unknown length-delimited field (the pad), strict
+    if (t < 0x80u && ((S.skip_unk_mask >> (t >> 3)) & 1u) && (t & 7u) == 2u) {
+      const uint32_t pl = (x >> 8) & 0xFFu;
+      d += 2u + pl;
+      if (pl >= 0x80u || d + 4u > len) return false;
+      x = rd4(d);
+    }
+  }
+  if ((x & 0x80FF80FFu) != (S.tag_status | (S.tag_value << 16))) return false;
+  status = (x >> 8) & 0x7Fu; uval = x >> 24;
+  d += 4u;
+  if (d != len) {                                            // one trailing field that ends the message
+    if (d + 2u > len) return false;
+    const uint32_t y = rd4(d), t = y & 0xFFu, n = (y >> 8) & 0xFFu;
+    if (t >= 0x80u || n >= 0x80u) return false;
+    const bool str = (S.skip_str_mask >> (t >> 3)) & 1u, unk = ((S.skip_unk_mask >> (t >> 3)) & 1u) && (t & 7u) == 2u;
+    const uint32_t after = d + 2u + n;
+    if (!(str ? after >= len : (unk && after == len))) return false;      // string() clamps to the end, skip() is strict
+  }
+  if (!key_is_string) { kh = (uint64_t)status; return true; }            // reference mode: the key is the status itself
+  // key hash (bh_common.cuh): 8-byte words of the key bytes, then the length word, then the status word
+  uint64_t h = S.hash_seed ^ kHashInit;
+  uint32_t wa = w0, a = m + 4u, i = 0;
+#pragma unroll 1
+  for (; i + 8u <= klen; i += 8u) {
+    const uint32_t wb = lds32(a), wc = lds32(a + 4u);
+    h = absorb(h, ((uint64_t)__funnelshift_r(wb, wc, 16) << 32) | __funnelshift_r(wa, wb, 16));
+    wa = wc; a += 8u;
+  }
+  if (i < klen) {
+    const uint32_t wb = lds32(a), wc = lds32(a + 4u);      // may read past the key: masked
+    const uint64_t w = ((uint64_t)__funnelshift_r(wb, wc, 16) << 32) | __funnelshift_r(wa, wb, 16);
+    h = absorb(h, w & ((1ull << (8u * (klen - i))) - 1ull));
+  }
+  h = absorb(h, len_word(klen, S.part_fld(0)));
+  if (S.n_parts == 2) h = absorb(h, varint_word(status, S.part_fld(1)));
+  kh = fmix64(h);
+  return true;
+}
+
 template <class SC>
 __device__ __forceinline__ uint32_t decode_and_check_smem(const SC& S, const SmemRd& r, uint32_t len, uint64_t& kh,
                                                           double& value, int32_t& ival, uint32_t& status, uint32_t mask) {
   Parsed P;
   uint32_t slow = 0;
+#ifndef BH_NO_BLOCK_TIER
+  {
+    uint32_t st = 0, uv = 0;
+    const bool blk = decode_block(S, r, len, kh, st, uv);
+    mask = __ballot_sync(mask, !blk);                      // the lanes that go on to the tiers below, together
+    if (blk) {
+      P.status = st; P.uval = uv; P.value = 0.0;
+      return finish_event(S, P, value, ival, status);
+    }
+  }
+#endif
 #ifdef BH_NO_TIER0
   const bool canon = false;
 #else
