@@ -99,6 +99,8 @@ PROTOTYPES = {
     "bh_set_commit_callback": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),
     "bh_host_alloc": (C.c_int, [C.POINTER(C.c_void_p), C.c_size_t]),
     "bh_host_free": (C.c_int, [C.c_void_p]),
+    "bh_host_register": (C.c_int, [C.c_void_p, C.c_size_t]),
+    "bh_host_unregister": (C.c_int, [C.c_void_p]),
     "bh_snapshot": (C.c_int, [C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64)]),
     "bh_snapshot_hist": (C.c_int, [C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64)]),
     "bh_list_windows": (C.c_int, [C.c_void_p, _u64p, C.c_uint32, C.POINTER(C.c_uint32)]),

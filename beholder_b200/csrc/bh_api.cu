@@ -274,7 +274,8 @@ int submit_current(bh_ctx* c) {
 void ring_copy(uint8_t* dst, const uint8_t* src, size_t n) {
   constexpr size_t kParallelFrom = 8u << 20;
   static const unsigned hw = std::max(1u, std::thread::hardware_concurrency());
-  const unsigned nt = n < kParallelFrom ? 1u : std::min<unsigned>({8u, std::max(1u, hw / 2), (unsigned)(n / (2u << 20))});
+  static const unsigned cap = [] { const char* e = getenv("BEHOLDER_COPY_THREADS"); int v = e ? atoi(e) : 0; return v > 0 ? (unsigned)v : 8u; }();
+  const unsigned nt = n < kParallelFrom ? 1u : std::min<unsigned>({cap, std::max(1u, hw / 2), (unsigned)(n / (2u << 20))});
   if (nt <= 1) { memcpy(dst, src, n); return; }
   std::vector<std::thread> th;
   const size_t part = ((n + nt - 1) / nt + 4095) & ~(size_t)4095;
@@ -284,6 +285,18 @@ void ring_copy(uint8_t* dst, const uint8_t* src, size_t n) {
   }
   memcpy(dst, src, std::min(n, part));
   for (auto& t : th) t.join();
+}
+
+// offsets of a caller-owned batch: non-decreasing?  (The kernels bound every read by the batch's last offset, so a
+// corrupt table would send them outside the slab.)  50 MB of offsets per 12.5 M events: on a few threads.
+bool offsets_monotone(const uint32_t* off, uint64_t n) {
+  auto scan = [off](uint64_t lo, uint64_t hi) { uint32_t bad = 0; for (uint64_t i = lo; i < hi; i++) bad |= off[i + 1] < off[i]; return bad == 0; };
+  if (n < (1u << 20)) return scan(0, n);
+  const unsigned nt = std::min(8u, std::max(1u, std::thread::hardware_concurrency() / 2));
+  std::vector<std::thread> th; std::vector<char> ok(nt, 1);
+  for (unsigned t = 0; t < nt; t++) th.emplace_back([&, t] { ok[t] = scan(n * t / nt, n * (t + 1) / nt); });
+  for (auto& t : th) t.join();
+  return std::all_of(ok.begin(), ok.end(), [](char c) { return c != 0; });
 }
 
 // the partial slab just received its first message: start its deadline, wake the completion thread
@@ -556,6 +569,17 @@ int bh_host_alloc(void** out, size_t bytes) {
 }
 int bh_host_free(void* p) { return cudaFreeHost(p) == cudaSuccess ? BH_OK : BH_ERR_CUDA; }
 
+int bh_host_register(void* p, size_t bytes) {
+  if (!p || !bytes) return BH_ERR_INVALID;
+  cudaError_t e = cudaHostRegister(p, bytes, cudaHostRegisterPortable);
+  if (e != cudaSuccess) { g_create_error = cudaGetErrorString(e); cudaGetLastError(); return e == cudaErrorMemoryAllocation ? BH_ERR_NOMEM : BH_ERR_CUDA; }
+  return BH_OK;
+}
+int bh_host_unregister(void* p) {
+  if (cudaHostUnregister(p) != cudaSuccess) { cudaGetLastError(); return BH_ERR_CUDA; }
+  return BH_OK;
+}
+
 int bh_push(bh_ctx* c, const uint8_t* payload, uint32_t len, uint64_t ts_ms) {
   if (!c || (!payload && len)) return fail(c, BH_ERR_INVALID, "null argument");
   if ((uint64_t)len > c->slab_bytes) return fail(c, BH_ERR_TOO_LARGE, "message of %u bytes exceeds slab_bytes %llu", len, (unsigned long long)c->slab_bytes);
@@ -619,6 +643,7 @@ int bh_push_batch(bh_ctx* c, const uint8_t* slab, const uint32_t* off, const uin
 int bh_push_batch_pinned(bh_ctx* c, const uint8_t* slab, const uint32_t* off, const uint64_t* ts, uint32_t n) {
   if (!c || (n && (!slab || !off))) return fail(c, BH_ERR_INVALID, "null argument");
   if (c->S.has_window && !ts && n) return fail(c, BH_ERR_INVALID, "ts_ms required in windowed mode");
+  if (n && !offsets_monotone(off, n)) return fail(c, BH_ERR_INVALID, "offsets must not decrease");
   BH_LOCK(c);
   DeviceGuard guard(c->device);
   // keep arrival order: anything staged through bh_push goes first
@@ -723,7 +748,7 @@ int bh_set_commit_callback(bh_ctx* c, bh_commit_cb cb, void* user) {
   return BH_OK;
 }
 
-static int ensure_export(bh_ctx* c, uint64_t cap, bool hist);
+static int ensure_export(bh_ctx* c, uint64_t cap, bool hist, bool all_windows);
 
 // host-pointer merge: the restore side of bh_snapshot_hist
 int bh_restore(bh_ctx* c, const bh_record* recs, const uint32_t* hist, uint64_t n) {
@@ -734,7 +759,7 @@ int bh_restore(bh_ctx* c, const bh_record* recs, const uint32_t* hist, uint64_t 
   if (rc) return rc;
   const uint64_t chunk = 1u << 16;
   bool with_hist = hist != nullptr && c->T.hist != nullptr;
-  rc = ensure_export(c, std::min<uint64_t>(std::max<uint64_t>(n, 1), chunk), with_hist);
+  rc = ensure_export(c, std::min<uint64_t>(std::max<uint64_t>(n, 1), chunk), with_hist, false);
   if (rc) return rc;
   for (uint64_t i = 0; i < n; i += c->export_cap) {
     uint64_t m = std::min<uint64_t>(c->export_cap, n - i);
@@ -786,15 +811,16 @@ int bh_flush(bh_ctx* c, uint64_t* committed_seq) {
   return rc;
 }
 
-static int ensure_export(bh_ctx* c, uint64_t cap, bool hist) {
-  if (cap > c->T.stride) cap = c->T.stride;
+static int ensure_export(bh_ctx* c, uint64_t cap, bool hist, bool all_windows) {
+  const uint64_t most = all_windows ? c->T.stride * c->T.ring : c->T.stride;    // rows a snapshot can return
+  if (cap > most) cap = most;
   if (cap == 0) cap = 1;
   if (cap > c->export_cap) {
     if (c->d_export) cudaFree(c->d_export);
     if (c->d_export_hist) cudaFree(c->d_export_hist);
     c->d_export = nullptr; c->d_export_hist = nullptr; c->export_cap = 0;
     CU(c, cudaMalloc((void**)&c->d_export, cap * sizeof(bh_record)));
-    c->export_cap = cap;
+    c->export_cap = cap;      // (d_export_hist was freed above and is re-made at the new size below)
   }
   if (hist && c->T.hist && !c->d_export_hist)
     CU(c, cudaMalloc((void**)&c->d_export_hist, c->export_cap * c->T.hist_buckets * 4));
@@ -808,7 +834,7 @@ int bh_snapshot_hist(bh_ctx* c, uint64_t window_id, bh_record* out, uint32_t* hi
   int rc = submit_current(c);
   if (rc) return rc;
   bool hist = hist_out != nullptr && c->T.hist != nullptr;
-  rc = ensure_export(c, cap, hist);
+  rc = ensure_export(c, cap, hist, window_id == BH_ALL_WINDOWS);
   if (rc) return rc;
   uint64_t dcap = std::min<uint64_t>(cap, c->export_cap);
   rc = part_drain(c, c->st_compute);

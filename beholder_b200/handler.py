@@ -35,7 +35,7 @@ from typing import Awaitable, Callable, Deque, Dict, List, Optional, Tuple
 
 from . import _lib as L
 from .engine import Aggregator
-from .schema import Schema, telemetry_progress, telemetry_status
+from .schema import Schema, decode_message, telemetry_progress, telemetry_status
 
 COUNTER_NAME = "beholder_progress_updates_total"                                       # index.js:31
 COUNTER_HELP = "Total number of messages processed in this processes lifetime"         # index.js:32
@@ -103,6 +103,14 @@ class BeholderGPU:
         self.trello_comments_total = HostCounter("beholder_trello_comments",
                                                  "Total trello comments crreated in this processes lifetime")
 
+    def _reaches_side_effects(self, content) -> bool:
+        """The reference reaches db.getByID and the Trello comment (index.js:140-148) only after proto.decode
+        (:129) and enumToString(...).toLowerCase() (:134,137) succeeded; a message that does not decode, or whose
+        status has no enum name, goes to the catch (:149) with no side effect.  Same gate here, decided on the host
+        for this one message (the GPU decodes the same bytes for the counters)."""
+        msg = decode_message(self.schema, bytes(content))
+        return msg is not None and self.schema.enum_name(msg.get("status", 0)) is not None
+
     def _init_ack_state(self, prefetch: int):
         self._pending: Deque[Tuple[int, object]] = collections.deque()   # (sequence number, rmsg)
         self._seq = 0
@@ -132,7 +140,7 @@ class BeholderGPU:
             self._seq += 1
             self._unsubmitted += 1
             self._pending.append((self._seq, rmsg))
-            if side_effects is not None:
+            if side_effects is not None and self._reaches_side_effects(content):
                 # index.js:140-148 stay on the host, per event; their failure neither un-counts the
                 # event nor stops the ack (index.js:149-152)
                 try:

@@ -125,3 +125,107 @@ def encode(schema: Schema, **values) -> bytes:
         else:
             raise ValueError(f.kind)
     return bytes(out)
+
+
+# ---- host-side decode of ONE message (handler glue only: which messages reach the side effects) ----
+class _Reader:
+    """protobufjs 6.8.8 Reader / BufferReader on a Python bytes object: uint32() takes 5 value bytes, assumes a
+    longer varint is 10 bytes long and treats bytes past the end as continuation bytes; string() clamps to the
+    end of the buffer (Node Buffer), bytes() and the fixed-width reads throw past it."""
+
+    def __init__(self, buf: bytes):
+        self.buf, self.pos, self.len = buf, 0, len(buf)
+
+    def _peek(self, pos: int) -> int:
+        return self.buf[pos] if pos < self.len else 0x80
+
+    def uint32(self) -> int:
+        value = 0
+        for i in range(5):
+            b = self._peek(self.pos); self.pos += 1
+            value |= (b & (15 if i == 4 else 127)) << (7 * i)
+            if b < 128:
+                return value & 0xFFFFFFFF
+        self.pos += 5
+        if self.pos > self.len:
+            self.pos = self.len
+            raise IndexError("index out of range")
+        return value & 0xFFFFFFFF
+
+    def skip(self, n: Optional[int] = None) -> None:
+        if n is None:
+            while True:
+                if self.pos >= self.len:
+                    raise IndexError("index out of range")
+                b = self.buf[self.pos]; self.pos += 1
+                if not b & 128:
+                    return
+        if self.pos + n > self.len:
+            raise IndexError("index out of range")
+        self.pos += n
+
+    def skip_type(self, wire: int) -> None:
+        depth = 0
+        while True:
+            if wire == 0:
+                self.skip()
+            elif wire == 1:
+                self.skip(8)
+            elif wire == 2:
+                self.skip(self.uint32())
+            elif wire == 3:
+                depth += 1
+            elif wire == 5:
+                self.skip(4)
+            elif wire == 4 and depth > 0:
+                depth -= 1
+            else:
+                raise ValueError("invalid wire type")
+            if depth == 0:
+                return
+            wire = self.uint32() & 7
+
+
+def decode_message(schema: Schema, buf: bytes) -> Optional[dict]:
+    """What `proto.decode(type, content)` (index.js:129) yields for the fields of `schema`, or None where it
+    throws.  Host code for the handler glue (the GPU decodes the same bytes for the counters): it decides whether a
+    delivery reaches the per-event side effects of index.js:140-148, which the reference only runs for messages
+    that decoded and whose status has an enum name."""
+    import struct
+    by_number = {f.number: f for f in schema.fields}
+    out = {f.name: (b"" if f.kind in (L.K_STRING, L.K_BYTES) else 0) for f in schema.fields}     # strings as their raw bytes
+    r = _Reader(bytes(buf))
+    try:
+        while r.pos < r.len:
+            t = r.uint32()
+            f = by_number.get(t >> 3)
+            if f is None:
+                r.skip_type(t & 7)
+                continue
+            if f.kind in (L.K_STRING, L.K_BYTES):
+                n = r.uint32()
+                end = r.pos + n
+                if end > r.len:
+                    if f.kind == L.K_BYTES:
+                        raise IndexError("index out of range")
+                    end = r.len
+                out[f.name] = r.buf[r.pos:end]
+                r.pos = end
+            elif f.kind in (L.K_INT32, L.K_UINT32, L.K_SINT32, L.K_BOOL):
+                u = r.uint32()
+                if f.kind == L.K_SINT32:
+                    u = ((u >> 1) ^ -(u & 1)) & 0xFFFFFFFF
+                if f.kind == L.K_BOOL:
+                    u = int(u != 0)
+                out[f.name] = u if f.kind in (L.K_UINT32, L.K_BOOL) else (u - (1 << 32) if u & 0x80000000 else u)
+            elif f.kind == L.K_FLOAT:
+                if r.pos + 4 > r.len:
+                    raise IndexError("index out of range")
+                out[f.name] = struct.unpack_from("<f", r.buf, r.pos)[0]; r.pos += 4
+            else:
+                if r.pos + 8 > r.len:
+                    raise IndexError("index out of range")
+                out[f.name] = struct.unpack_from("<d", r.buf, r.pos)[0]; r.pos += 8
+    except (IndexError, ValueError):
+        return None
+    return out

@@ -166,6 +166,13 @@ typedef void (*bh_commit_cb)(void* user, uint64_t committed_seq);
 int bh_set_commit_callback(bh_ctx* ctx, bh_commit_cb cb, void* user);
 int bh_host_alloc(void** out, size_t bytes);   /* pinned host memory for bh_push_batch_pinned */
 int bh_host_free(void* p);
+/* Page-lock memory the caller already owns (a pool of Node Buffers that is reused, an mmap'ed capture file), so
+ * that bh_push_batch_pinned can take it: the GPU then reads it in place and the copy into the library's ring --
+ * the limit of bh_push_batch from ordinary memory, one pass over host DRAM at memcpy speed -- disappears.
+ * Registering costs on the order of a millisecond per 10 MB: do it once per buffer, not per batch.  The memory
+ * must stay mapped until bh_host_unregister. */
+int bh_host_register(void* p, size_t bytes);
+int bh_host_unregister(void* p);
 
 /* ---- read side: what Prom.expose() serves (index.js:28) ---- */
 /* rows of one window (REFERENCE mode: window 0) in unspecified order; *n = rows available */

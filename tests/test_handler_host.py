@@ -83,10 +83,44 @@ def test_side_effect_errors_are_caught_like_index_js_149():
         seen.append(rmsg.message.content)
         raise ValueError("trello down")
     amqp.listen("v1.telemetry.progress", g.handler(side))
-    amqp.publish("v1.telemetry.progress", b"a"); amqp.publish("v1.telemetry.progress", b"b")
+    a = bh.encode(g.schema, mediaId="a", status=4, progress=1); b = bh.encode(g.schema, mediaId="b", status=5, progress=2)
+    amqp.publish("v1.telemetry.progress", a); amqp.publish("v1.telemetry.progress", b)
     asyncio.run(amqp.run())
     g.commit()
-    assert seen == [b"a", b"b"] and amqp.acked == 2 and g.agg.pushed == [b"a", b"b"]
+    assert seen == [a, b] and amqp.acked == 2 and g.agg.pushed == [a, b]
+
+
+def test_side_effects_only_for_messages_the_reference_would_have_processed():
+    # index.js:129-137: a message that does not decode, or whose status has no enum name, lands in the catch
+    # before db.getByID / the Trello comment (:140-148): no side effect, still counted as received and acked
+    amqp = bh.StubAMQP()
+    g = _gpu(commit_every=100)
+    seen = []
+    amqp.listen("v1.telemetry.progress", g.handler(lambda rmsg: seen.append(rmsg.message.content)))
+    good = bh.encode(g.schema, mediaId="m", status=4, progress=7)
+    unknown_enum = bh.encode(g.schema, mediaId="m", status=99, progress=7)
+    truncated = good[:-1] + b"\x80"                      # the last varint never ends
+    bad_wire = b"\x4f" + good                            # unknown field 9 with wire type 7: skipType throws
+    for m in (good, unknown_enum, truncated, bad_wire, good):
+        amqp.publish("v1.telemetry.progress", m)
+    asyncio.run(amqp.run())
+    g.commit()
+    assert seen == [good, good] and amqp.acked == 5 and len(g.agg.pushed) == 5
+
+
+def test_host_decoder_agrees_with_the_known_answer_messages():
+    import json, os
+    from beholder_b200.schema import decode_message
+    from beholder_b200 import _lib as L
+    kat = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "kat_decode.json")))
+    s = bh.telemetry_progress()
+    for c in kat["default"]:
+        m = decode_message(s, bytes.fromhex(c["payload"]))
+        assert (m is None) == (c["outcome"] == L.EV_DROP_DECODE), c["name"]
+        if m is not None:
+            assert m["status"] == c["status"] and bytes(m["mediaId"]).hex() == c["media_id"], c["name"]
+            if c["outcome"] == L.EV_OK:
+                assert float(m["progress"]) == c["value"], c["name"]
 
 
 def test_counter_shape_matches_prom_client():

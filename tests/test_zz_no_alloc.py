@@ -79,3 +79,24 @@ def test_static_export_refuses_more_owners_than_its_scratch_holds():
         with pytest.raises(bh.BeholderError) as e:
             g.export_window_static(L.BH_ALL_WINDOWS, 2 * L.BH_STATIC_EXPORT_MAX_OWNERS, recs, None, 16, counts)
         assert e.value.code == L.BH_ERR_TOO_LARGE and "built-in scratch" in str(e.value)
+
+
+def test_static_export_leaves_the_free_device_memory_unchanged():
+    """what the entry point exists for, measured: the driver reports the same number of free bytes after the
+    calls as before them (outputs allocated beforehand by the caller, as the contract says)"""
+    import torch
+    n = 100_000
+    p, o, t, _ = generate_device(SynthSpec(n_keys=2000, rate_per_ms=10), 0, n)
+    with bh.Aggregator(mode=L.MODE_WINDOWED, ops=ALL_OPS, table_capacity=8192, window_ring=8) as g:
+        g.process_device(p, o, t, n)
+        g.sync()
+        recs = torch.zeros(20_000, 6, dtype=torch.int64, device="cuda")
+        counts = torch.zeros(8, dtype=torch.int64, device="cuda")
+        g.export_window_static(L.BH_ALL_WINDOWS, 8, recs, None, 20_000, counts)     # first call on this device: address look-up
+        g.sync(); torch.cuda.synchronize()
+        free_before = torch.cuda.mem_get_info()[0]
+        for n_owners in (8, 4, 1):
+            g.export_window_static(L.BH_ALL_WINDOWS, n_owners, recs, None, 20_000, counts)
+        g.sync(); torch.cuda.synchronize()
+        assert torch.cuda.mem_get_info()[0] == free_before
+        assert int(counts.cpu()[0]) > 0
