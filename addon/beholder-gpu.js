@@ -15,7 +15,7 @@ const ROLE = { key: 1, status: 2, value: 4 }
 
 // Byte offsets inside bh_config (include/beholder_gpu.h), little endian.  tests/test_abi.py compiles the
 // header, prints offsetof() for every name below and fails when this table and the C struct disagree.
-const OFF = { struct_size: 0, device: 4, mode: 8, ops: 12, n_fields: 36, fields: 40, n_enum: 296, enum_numbers: 300, max_batch_latency_ms: 600, SIZE: 608, FIELD_SIZE: 16 }
+const OFF = { struct_size: 0, device: 4, mode: 8, ops: 12, n_fields: 36, fields: 40, n_enum: 296, enum_numbers: 300, max_batch_latency_ms: 600, SIZE: 616, FIELD_SIZE: 16 }
 
 function packConfig ({ schema, statusEnum, device = 0, maxBatchLatencyMs = 5 }) {
   const buf = Buffer.alloc(OFF.SIZE)

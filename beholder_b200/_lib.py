@@ -29,7 +29,9 @@ BH_ERR_TABLE_FULL = -5
 BH_ERR_WINDOW_RING = -6
 BH_ERR_TOO_LARGE = -7
 BH_ERR_UNSUPPORTED = -8
+BH_ERR_KEY_COLLISION = -9
 STATUS_NAMES = {
+    -9: "BH_ERR_KEY_COLLISION",
     0: "BH_OK", -1: "BH_ERR_INVALID", -2: "BH_ERR_NO_DEVICE", -3: "BH_ERR_CUDA", -4: "BH_ERR_NOMEM",
     -5: "BH_ERR_TABLE_FULL", -6: "BH_ERR_WINDOW_RING", -7: "BH_ERR_TOO_LARGE", -8: "BH_ERR_UNSUPPORTED",
 }
@@ -38,7 +40,7 @@ STATUS_NAMES = {
 K_STRING, K_BYTES, K_INT32, K_UINT32, K_SINT32, K_BOOL, K_FLOAT, K_DOUBLE = range(1, 9)
 R_KEY, R_STATUS, R_VALUE = 1, 2, 4
 OP_COUNT, OP_SUM, OP_MIN, OP_MAX, OP_HIST = 1, 2, 4, 8, 16
-F_GENERIC_KERNELS, F_NO_NUMA_BIND, F_PARTITIONED, F_NO_PARTITION = 1, 2, 4, 8   # bh_config.flags
+F_GENERIC_KERNELS, F_NO_NUMA_BIND, F_PARTITIONED, F_NO_PARTITION, F_VERIFY_KEYS = 1, 2, 4, 8, 16   # bh_config.flags
 MODE_REFERENCE, MODE_WINDOWED = 0, 1
 EV_OK, EV_DROP_DECODE, EV_DROP_ENUM, EV_DROP_NAN = 0, 1, 2, 3
 
@@ -55,7 +57,7 @@ class BhConfig(C.Structure):
         ("n_enum", C.c_uint32), ("enum_numbers", C.c_int32 * BH_MAX_ENUM),
         ("table_capacity", C.c_uint64), ("hash_seed", C.c_uint64), ("slab_bytes", C.c_uint64),
         ("slab_events", C.c_uint32), ("n_slabs", C.c_uint32), ("message_bytes_hint", C.c_uint32), ("flags", C.c_uint32),
-        ("max_batch_latency_ms", C.c_uint32), ("part_region_tuples", C.c_uint32),
+        ("max_batch_latency_ms", C.c_uint32), ("part_region_tuples", C.c_uint32), ("debug_hash_mask", C.c_uint64),
     ]
 
 
@@ -67,7 +69,7 @@ class BhRecord(C.Structure):
 class BhCounters(C.Structure):
     _fields_ = [("events_ok", C.c_uint64), ("dropped_decode", C.c_uint64), ("dropped_enum", C.c_uint64),
                 ("dropped_nan", C.c_uint64), ("dropped_table_full", C.c_uint64), ("dropped_window", C.c_uint64),
-                ("smem_spills", C.c_uint64), ("slow_decodes", C.c_uint64)]
+                ("smem_spills", C.c_uint64), ("slow_decodes", C.c_uint64), ("key_collisions", C.c_uint64)]
 
 
 class BhSynthConfig(C.Structure):

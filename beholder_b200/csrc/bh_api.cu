@@ -171,6 +171,7 @@ int build_schema(const bh_config& cfg, DevSchema& S) {
   if (S.hist_buckets < 2 || S.hist_buckets > BH_HIST_MAX) return fail(nullptr, BH_ERR_INVALID, "hist_buckets must be 2..%d", BH_HIST_MAX);
   S.hist_e0 = cfg.hist_e0;
   S.hash_seed = cfg.hash_seed;
+  S.hash_mask = cfg.debug_hash_mask ? cfg.debug_hash_mask : ~0ull;
   S.has_window = cfg.mode == BH_MODE_WINDOWED && cfg.window_ms > 0;
   if (S.has_window) S.wdiv = make_div64(cfg.window_ms);
   return BH_OK;
@@ -246,6 +247,7 @@ int slab_launch(bh_ctx* c, Slab& s, const uint8_t* virt, uint32_t n, bool with_t
   // the ingest path knows the slab's byte count: pick the kernel variant from the real average size
   CU(c, launch_process_raw(c->S, c->T, c->G, virt, s.d_offsets, with_ts ? s.d_ts : nullptr, n, c->st_compute, &c->launches,
                            n && bytes / n > 72 ? 1 : 0));
+  CU(c, launch_verify_keys(c->S, c->T, c->G, virt, s.d_offsets, n, c->st_compute, n && bytes / n > 72 ? 1 : 0));
   CU(c, cudaEventRecord(s.done, c->st_compute));
   s.in_flight = true;
   s.seq_end = c->pushed;
@@ -428,8 +430,10 @@ struct NumaLocalGuard {
 int counters_status(const bh_counters& k) {
   if (k.dropped_table_full) return BH_ERR_TABLE_FULL;
   if (k.dropped_window) return BH_ERR_WINDOW_RING;
+  if (k.key_collisions) return BH_ERR_KEY_COLLISION;
   return BH_OK;
 }
+static_assert(sizeof(bh_counters) == kCounters * 8, "bh_counters and the device counter array");
 
 }  // namespace
 
@@ -490,7 +494,14 @@ int bh_create(const bh_config* cfg, bh_ctx** out) {
   CUB_(cudaMalloc((void**)&T.keys, rows * 8));
   CUB_(cudaMalloc((void**)&T.stats, rows * sizeof(Stat)));
   if (S.ops & BH_OP_HIST) CUB_(cudaMalloc((void**)&T.hist, rows * S.hist_buckets * 4));
-  CUB_(cudaMalloc((void**)&T.counters, 8 * 8));
+  CUB_(cudaMalloc((void**)&T.counters, kCounterSlots * 8));
+  if (cfg->flags & BH_F_VERIFY_KEYS) {
+    const bool ok_shape = cfg->mode == BH_MODE_WINDOWED && S.fast_key0 != 0xFFFFFFFFu &&
+                          (S.n_parts == 1 || (S.n_parts == 2 && S.fast_status_part == 2));
+    if (!ok_shape) { fail(c, BH_ERR_UNSUPPORTED, "BH_F_VERIFY_KEYS needs a windowed context keyed by one string field, optionally followed by the status"); return bail(BH_ERR_UNSUPPORTED); }
+    T.dict_cap = 2 * cap;
+    CUB_(cudaMalloc((void**)&T.dict, T.dict_cap * sizeof(DictEntry)));
+  }
   // partitioned (deferred) aggregation: on request, or by itself once a window's table is too large for L2
   const bool part = cfg->mode == BH_MODE_WINDOWED && !(cfg->flags & BH_F_NO_PARTITION) &&
                     ((cfg->flags & BH_F_PARTITIONED) || cap >= (1ull << 18));
@@ -544,6 +555,7 @@ void bh_destroy(bh_ctx* c) {
   if (c->T.stats) cudaFree(c->T.stats);
   if (c->T.hist) cudaFree(c->T.hist);
   if (c->T.counters) cudaFree(c->T.counters);
+  if (c->T.dict) cudaFree(c->T.dict);
   if (c->T.part_tuples) cudaFree(c->T.part_tuples);
   if (c->T.part_fill) cudaFree(c->T.part_fill);
   if (c->part_ev) cudaEventDestroy(c->part_ev);
@@ -679,6 +691,7 @@ int bh_push_batch_pinned(bh_ctx* c, const uint8_t* slab, const uint32_t* off, co
 int bh_push_columns(bh_ctx* c, const uint64_t* kh, const uint64_t* ts, const double* val, uint64_t n) {
   if (!c || (n && !kh)) return fail(c, BH_ERR_INVALID, "null argument");
   if (c->S.mode != BH_MODE_WINDOWED) return fail(c, BH_ERR_INVALID, "bh_push_columns needs BH_MODE_WINDOWED");
+  if (c->T.dict) return fail(c, BH_ERR_UNSUPPORTED, "BH_F_VERIFY_KEYS: pre-hashed columns carry no key bytes to verify");
   if (c->S.has_window && !ts && n) return fail(c, BH_ERR_INVALID, "ts_ms required in windowed mode");
   BH_LOCK(c);
   DeviceGuard guard(c->device);
@@ -788,7 +801,7 @@ int bh_get_counters(bh_ctx* c, bh_counters* out) {
   BH_LOCK(c);
   DeviceGuard guard(c->device);
   { int rc = part_drain(c, c->st_compute); if (rc) return rc; }
-  CU(c, cudaMemcpyAsync(c->h_small, c->T.counters, 8 * 8, cudaMemcpyDeviceToHost, c->st_compute));
+  CU(c, cudaMemcpyAsync(c->h_small, c->T.counters, kCounters * 8, cudaMemcpyDeviceToHost, c->st_compute));
   CU(c, cudaStreamSynchronize(c->st_compute));
   memcpy(out, c->h_small, sizeof(bh_counters));
   return counters_status(*out);
@@ -808,6 +821,7 @@ int bh_flush(bh_ctx* c, uint64_t* committed_seq) {
   rc = bh_get_counters(c, &k);
   if (rc == BH_ERR_TABLE_FULL) return fail(c, rc, "%llu events dropped: a window's key table is full (table_capacity %llu)", (unsigned long long)k.dropped_table_full, (unsigned long long)c->T.cap);
   if (rc == BH_ERR_WINDOW_RING) return fail(c, rc, "%llu events dropped: more than %u windows open (close windows or raise window_ring)", (unsigned long long)k.dropped_window, c->T.ring);
+  if (rc == BH_ERR_KEY_COLLISION) return fail(c, rc, "%llu events carry a key whose 64-bit hash belongs to a different key: their rows are merged with that key's (change hash_seed)", (unsigned long long)k.key_collisions);
   return rc;
 }
 
@@ -896,6 +910,7 @@ int bh_process_device(bh_ctx* c, const uint8_t* d_payload, const uint32_t* d_off
   cudaStream_t st = stream ? (cudaStream_t)stream : c->st_compute;
   { int rc = part_reserve(c, n, st, false); if (rc) return rc; }
   CU(c, launch_process_raw(c->S, c->T, c->G, d_payload, d_offsets, d_ts, n, st, &c->launches));
+  CU(c, launch_verify_keys(c->S, c->T, c->G, d_payload, d_offsets, n, st));
   return BH_OK;
 }
 
@@ -903,6 +918,7 @@ int bh_process_columns_device(bh_ctx* c, const uint64_t* d_kh, const uint64_t* d
                               uint64_t n, void* stream) {
   if (!c || (n && !d_kh)) return fail(c, BH_ERR_INVALID, "null argument");
   if (c->S.mode != BH_MODE_WINDOWED) return fail(c, BH_ERR_INVALID, "needs BH_MODE_WINDOWED");
+  if (c->T.dict) return fail(c, BH_ERR_UNSUPPORTED, "BH_F_VERIFY_KEYS: pre-hashed columns carry no key bytes to verify");
   if (c->S.has_window && !d_ts && n) return fail(c, BH_ERR_INVALID, "d_ts_ms required in windowed mode");
   BH_LOCK(c);
   DeviceGuard guard(c->device);

@@ -122,6 +122,7 @@ struct DevSchema {
   uint32_t hist_buckets;
   int32_t hist_e0;
   uint64_t hash_seed;
+  uint64_t hash_mask;     // ANDed onto every key hash (all ones unless the debug_hash_mask test hook is set)
   uint32_t has_window;
   uint32_t int_values;    // the VALUE field is int32 / sint32 / bool (or absent): integer shared-memory table
   // fields the fast decoder recognises by number (0xFFFFFFFF = not applicable)
@@ -152,6 +153,17 @@ constexpr uint64_t kEmptyKey = 0xFFFFFFFFFFFFFFFFull;  // never stored as a key:
 constexpr uint64_t kLockKey = 0xFFFFFFFFFFFFFFFEull;   // shared-memory table only
 constexpr uint64_t kNoWindow = 0xFFFFFFFFFFFFFFFFull;
 
+// BH_F_VERIFY_KEYS: per key hash, the key bytes first seen with it.  64 bytes = one entry.
+struct DictEntry {
+  unsigned long long kh;        // kEmptyKey: free
+  unsigned int ready;           // 0 while the winner of the slot is still writing
+  unsigned int len;             // bytes of the string key part
+  unsigned int status;          // value of the status key part (0 when the key has none)
+  unsigned int pad;
+  unsigned char bytes[40];      // the key bytes; longer keys: the first 32 bytes + an 8-byte hash of all of them
+};
+static_assert(sizeof(DictEntry) == 64, "one line");
+
 struct DevTables {
   unsigned long long* ring_win;  // [ring] window id held by each ring slot, kNoWindow = free
   unsigned long long* keys;      // [ring][stride]
@@ -174,9 +186,15 @@ struct DevTables {
   uint32_t part_cap;             // tuples per region
   uint32_t part_ctas;            // regions per partition = the largest grid of the scattering kernels
   uint32_t part_smem_off;        // where a scattering kernel keeps its P cursors in dynamic shared memory (set per launch)
+  DictEntry* dict;               // BH_F_VERIFY_KEYS, else nullptr
+  uint64_t dict_cap;             // power of two
 };
 
-enum CounterIdx { C_OK = 0, C_DECODE = 1, C_ENUM = 2, C_NAN = 3, C_TABLE_FULL = 4, C_WINDOW = 5, C_SPILL = 6, C_SLOW = 7 };
+enum CounterIdx { C_OK = 0, C_DECODE = 1, C_ENUM = 2, C_NAN = 3, C_TABLE_FULL = 4, C_WINDOW = 5, C_SPILL = 6, C_SLOW = 7, C_COLLISION = 8 };
+constexpr int kCounters = 9;       // sizeof(bh_counters) / 8
+constexpr int kCounterSlots = 16;  // u64 slots allocated for them
+
+
 
 // ---------------------------------------------------------------------------------------
 // splitmix64 and the synthetic stream, one definition for host and device

@@ -521,7 +521,7 @@ __device__ __forceinline__ uint64_t event_key_hash(const DevSchema& S, const R& 
       h = absorb(h, varint_word(P.pval[k], S.part_field[k]));
     }
   }
-  return fmix64(h);
+  return fmix64(h) & S.hash_mask;
 }
 
 // ---- fast path ---------------------------------------------------------------------------------
@@ -650,9 +650,9 @@ struct ProgressSchemaT {
   static constexpr uint32_t fast_value_f64 = 0, tag_key0 = REF ? 0xFFFFFFFFu : 0x0Au, tag_status = 0x10, tag_value = 0x18;
   static constexpr uint32_t skip_str_mask = REF ? ((1u << 1) | (1u << 4)) : (1u << 4), skip_unk_mask = 0xFFFFu & ~0x1Eu;
   // run-time items
-  uint32_t ops; uint64_t enum_mask, hash_seed; Div64 wdiv;
+  uint32_t ops; uint64_t enum_mask, hash_seed, hash_mask; Div64 wdiv;
   __device__ __forceinline__ explicit ProgressSchemaT(const DevSchema& S)
-      : dyn(S), ops(S.ops), enum_mask(S.enum_mask), hash_seed(S.hash_seed), wdiv(S.wdiv) {}
+      : dyn(S), ops(S.ops), enum_mask(S.enum_mask), hash_seed(S.hash_seed), hash_mask(S.hash_mask), wdiv(S.wdiv) {}
 };
 typedef ProgressSchemaT<false> ProgressSchema;
 
@@ -842,7 +842,7 @@ __device__ __forceinline__ uint64_t event_key_hash_smem(const SC& S, const SmemR
     if (S.part_len(k)) h = hash_span_smem(r, r.off + P.ppos[k], P.plen[k], S.part_fld(k), h);
     else h = absorb(h, varint_word(P.pval[k], S.part_fld(k)));
   }
-  return fmix64(h);
+  return fmix64(h) & S.hash_mask;
 }
 
 // drop rules after a successful decode.  Returns BH_EV_*.  `ival` is the value for integer value
@@ -871,7 +871,8 @@ __device__ __noinline__ bool decode_slow(const DevSchema& S, const SmemRd r, uin
 // made of that string and, optionally, the status.  That is a subset of what decode_canon accepts, with the same
 // field values by construction; anything else returns false with nothing decided and takes the tiers below.
 template <class SC>
-__device__ __forceinline__ bool decode_block(const SC& S, const SmemRd& r, uint32_t len, uint64_t& kh, uint32_t& status, uint32_t& uval) {
+__device__ __forceinline__ bool decode_block(const SC& S, const SmemRd& r, uint32_t len, uint64_t& kh, uint32_t& status, uint32_t& uval,
+                                             uint32_t& kloc) {
   if (S.fast_value_f64 || S.tag_status > 0x7Fu || S.tag_value > 0x7Fu || S.identity_key) return false;
   const bool key_is_string = S.tag_key0 <= 0x7Fu;
   if (key_is_string ? !(S.n_parts == 1 || (S.n_parts == 2 && S.fast_status_part == 2)) : !S.status_part) return false;
@@ -910,6 +911,7 @@ __device__ __forceinline__ bool decode_block(const SC& S, const SmemRd& r, uint3
     const uint32_t after = d + 2u + n;
     if (!(str ? after >= len : (unk && after == len))) return false;      // string() clamps to the end, skip() is strict
   }
+  kloc = 2u | (klen << 16);
   if (!key_is_string) { kh = (uint64_t)status; return true; }            // reference mode: the key is the status itself
   // key hash (bh_common.cuh): 8-byte words of the key bytes, then the length word, then the status word
   uint64_t h = S.hash_seed ^ kHashInit;
@@ -927,19 +929,23 @@ __device__ __forceinline__ bool decode_block(const SC& S, const SmemRd& r, uint3
   }
   h = absorb(h, len_word(klen, S.part_fld(0)));
   if (S.n_parts == 2) h = absorb(h, varint_word(status, S.part_fld(1)));
-  kh = fmix64(h);
+  kh = fmix64(h) & S.hash_mask;
   return true;
 }
 
+// kloc (for the key check of BH_F_VERIFY_KEYS; dead code elsewhere): position | length << 16 of the first key part's
+// bytes inside the message
 template <class SC>
 __device__ __forceinline__ uint32_t decode_and_check_smem(const SC& S, const SmemRd& r, uint32_t len, uint64_t& kh,
-                                                          double& value, int32_t& ival, uint32_t& status, uint32_t mask) {
+                                                          double& value, int32_t& ival, uint32_t& status, uint32_t mask,
+                                                          uint32_t& kloc) {
   Parsed P;
   uint32_t slow = 0;
+  kloc = 0;
 #ifndef BH_NO_BLOCK_TIER
   {
     uint32_t st = 0, uv = 0;
-    const bool blk = decode_block(S, r, len, kh, st, uv);
+    const bool blk = decode_block(S, r, len, kh, st, uv, kloc);
     mask = __ballot_sync(mask, !blk);                      // the lanes that go on to the tiers below, together
     if (blk) {
       P.status = st; P.uval = uv; P.value = 0.0;
@@ -960,18 +966,20 @@ __device__ __forceinline__ uint32_t decode_and_check_smem(const SC& S, const Sme
     slow = kSlowDecode;
   }
   kh = event_key_hash_smem(S, r, P);
+  kloc = P.ppos[0] | (P.plen[0] << 16);
   return finish_event(S, P, value, ival, status) | slow;
 }
 
 // Out of line (rare): results come back through one small object, so that the caller's own
 // kh/value/ival/status never have their address taken and stay in registers.
-struct EventOut { uint64_t kh; double value; int32_t ival; uint32_t status; };
+struct EventOut { uint64_t kh; double value; int32_t ival; uint32_t status; uint32_t kloc; };
 __device__ __noinline__ uint32_t decode_and_check_gmem(const DevSchema& S, const uint8_t* p, uint32_t len, EventOut& out) {
   Parsed P;
   GmemRd r{p};
-  out.kh = 0; out.value = 0.0; out.ival = 0; out.status = 0;
+  out.kh = 0; out.value = 0.0; out.ival = 0; out.status = 0; out.kloc = 0;
   if (!decode_event(S, r, len, P)) return BH_EV_DROP_DECODE;
   out.kh = event_key_hash(S, r, P);
+  out.kloc = P.ppos[0] | (P.plen[0] << 16);
   return finish_event(S, P, out.value, out.ival, out.status);
 }
 
@@ -1072,7 +1080,7 @@ __device__ __forceinline__ void raw_warp_loop(const SC& S, const uint8_t* __rest
     // in 2 parts of 16 messages (up to 144 B each) or 4 parts of 8 (up to 288 B) before falling back to
     // global memory.  Same results either way; the host picks the variant from the message-size hint.
     const bool sane = !valid || o1 >= o0;
-    uint32_t outcome = BH_EV_DROP_DECODE; uint64_t kh = 0; double value = 0.0; int32_t ival = 0; uint32_t status = 0;
+    uint32_t outcome = BH_EV_DROP_DECODE; uint64_t kh = 0; double value = 0.0; int32_t ival = 0; uint32_t status = 0, kloc = 0;
     uint32_t parts = 0;
 #pragma unroll
     for (uint32_t g = 32; g >= (BIG ? 8u : 32u) && parts == 0; g >>= 1) {
@@ -1088,16 +1096,16 @@ __device__ __forceinline__ void raw_warp_loop(const SC& S, const uint8_t* __rest
         __syncwarp();
         const bool mine = valid && (!BIG || (lane / g) == q);
         const uint32_t mask = __ballot_sync(0xFFFFFFFFu, mine);
-        if (mine) { SmemRd r{wb + (o0 - A)}; outcome = decode_and_check_smem(S, r, o1 - o0, kh, value, ival, status, mask); }
+        if (mine) { SmemRd r{wb + (o0 - A)}; outcome = decode_and_check_smem(S, r, o1 - o0, kh, value, ival, status, mask, kloc); }
         __syncwarp();                               // the buffer is rewritten by the next part / batch
         if (!BIG) break;
       }
     } else if (valid && sane) {
       EventOut out;
       outcome = decode_and_check_gmem(S, payload + o0, o1 - o0, out);
-      kh = out.kh; value = out.value; ival = out.ival; status = out.status;
+      kh = out.kh; value = out.value; ival = out.ival; status = out.status; kloc = out.kloc;
     }
-    sink.event(valid, e, outcome, kh, value, ival, status, aux);
+    sink.event(valid, e, outcome, kh, value, ival, status, aux, kloc);
   }
 }
 
@@ -1112,7 +1120,7 @@ struct AggSink {
     return (valid && S.has_window && ts) ? ts[e] : 0ull;
   }
   // called by the whole (converged) warp; `valid` marks the lanes that carry an event
-  __device__ __forceinline__ void event(bool valid, uint32_t, uint32_t outcome, uint64_t kh, double value, int32_t ival, uint32_t, uint64_t ts_ms) {
+  __device__ __forceinline__ void event(bool valid, uint32_t, uint32_t outcome, uint64_t kh, double value, int32_t ival, uint32_t, uint64_t ts_ms, uint32_t) {
     if (valid && (outcome & kSlowDecode)) C.bump(C_SLOW);
     outcome &= 0xFFu;
     if (valid && outcome != BH_EV_OK) C.bump(outcome);
@@ -1178,7 +1186,7 @@ struct ColumnSink {
   uint64_t* kh; double* val; int32_t* status; uint8_t* outcome;
   __device__ __forceinline__ void prefetch(uint32_t, uint32_t) const {}
   __device__ __forceinline__ uint64_t preload(uint32_t, bool) const { return 0ull; }
-  __device__ __forceinline__ void event(bool valid, uint32_t e, uint32_t oc, uint64_t k, double v, int32_t iv, uint32_t st, uint64_t) {
+  __device__ __forceinline__ void event(bool valid, uint32_t e, uint32_t oc, uint64_t k, double v, int32_t iv, uint32_t st, uint64_t, uint32_t) {
     if (!valid) return;
     // integer value kinds: the fast path leaves `v` unset; (double)(int32) is the JS number
     oc &= 0xFFu;
@@ -1204,6 +1212,87 @@ k_decode(const __grid_constant__ DevSchema S, const uint8_t* __restrict__ payloa
   if (cs >= ce) return;
   ColumnSink sink{S, kh, val, status, outcome};
   raw_warp_loop<BIG>(S, payload, offsets, cs, ce, wb, sink);
+}
+
+// =========================================================================================
+// BH_F_VERIFY_KEYS: full-key identity check (collisions detected, never silently merged)
+// =========================================================================================
+// The tables identify a key by its 64-bit hash.  This kernel decodes a batch again and, per event, looks the hash
+// up in a dictionary that keeps the key BYTES first seen with it (the winner of the slot writes them, everybody
+// else compares): a mismatch is a hash collision between two different keys and is counted.  Key bytes are read
+// from the payload in global memory (just staged, so from L2).
+struct VerifySink {
+  const DevSchema& S; const DevTables& T;
+  const uint8_t* payload; const uint32_t* offsets;
+  uint32_t collisions;
+  __device__ __forceinline__ void prefetch(uint32_t, uint32_t) const {}
+  __device__ __forceinline__ uint64_t preload(uint32_t, bool) const { return 0ull; }
+  __device__ __forceinline__ void event(bool valid, uint32_t e, uint32_t oc, uint64_t kh, double, int32_t, uint32_t status, uint64_t, uint32_t kloc) {
+    if (!valid || (oc & 0xFFu) != BH_EV_OK || kh >= kLockKey) return;
+    const uint32_t klen = kloc >> 16;
+    const GmemRd g{payload + offsets[e] + (kloc & 0xFFFFu)};
+    const uint32_t st = S.n_parts == 2 ? status : 0u;
+    // identity bytes: the key itself up to 40 bytes, else its first 32 bytes + a hash of all of it
+    uint64_t w[5];
+    if (klen <= 40u) {
+#pragma unroll
+      for (int i = 0; i < 5; i++) w[i] = g.le64(8u * i, klen > 8u * i ? klen - 8u * i : 0u);
+    } else {
+      uint64_t h = kHashInit;
+      for (uint32_t i = 0; i < klen; i += 8) h = absorb(h, g.le64(i, klen - i));
+#pragma unroll
+      for (int i = 0; i < 4; i++) w[i] = g.le64(8u * i, 8u);
+      w[4] = fmix64(h);
+    }
+    DictEntry* D = T.dict;
+    uint64_t slot = (kh * kHashMul) >> (64u - ilog2_u64(T.dict_cap));
+    for (uint64_t probes = 0; probes < T.dict_cap; probes++) {
+      unsigned long long k = *(volatile unsigned long long*)&D[slot].kh;
+      if (k == kEmptyKey) {
+        k = atomicCAS(&D[slot].kh, (unsigned long long)kEmptyKey, (unsigned long long)kh);
+        if (k == kEmptyKey) {                              // this lane owns the entry: write, then publish
+          D[slot].len = klen; D[slot].status = st;
+          unsigned long long* b = (unsigned long long*)D[slot].bytes;
+#pragma unroll
+          for (int i = 0; i < 5; i++) b[i] = w[i];
+          __threadfence();
+          *(volatile unsigned int*)&D[slot].ready = 1u;
+          return;
+        }
+      }
+      if (k == kh) {
+        while (*(volatile unsigned int*)&D[slot].ready == 0u) {}
+        __threadfence();
+        const unsigned long long* b = (const unsigned long long*)D[slot].bytes;
+        bool same = D[slot].len == klen && D[slot].status == st;
+#pragma unroll
+        for (int i = 0; i < 5; i++) same = same && __ldcg(b + i) == w[i];
+        if (!same) collisions++;
+        return;
+      }
+      slot = (slot + 1) & (T.dict_cap - 1);
+    }
+  }
+};
+
+template <bool BIG>
+__global__ void __launch_bounds__(kRawThreads, 1)
+k_verify_keys(const __grid_constant__ DevSchema S, const __grid_constant__ DevTables T, const uint8_t* __restrict__ payload,
+              const uint32_t* __restrict__ offsets, uint32_t n, uint32_t chunk) {
+  const uint32_t wb = warp_buffer_origin((uint32_t)__cvta_generic_to_shared(g_smem));
+#ifdef BH_BOUNDS_CHECK
+  if (threadIdx.x == 0) {
+    g_dbg_first = (uint32_t)__cvta_generic_to_shared(g_smem);
+    g_dbg_glo = payload; g_dbg_ghi = payload + ((offsets[n] + 15u) & ~15u);
+  }
+  __syncthreads();
+#endif
+  const uint32_t cs = min(n, blockIdx.x * chunk), ce = min(n, cs + chunk);
+  if (cs >= ce) return;
+  VerifySink sink{S, T, payload, offsets, 0u};
+  raw_warp_loop<BIG>(S, payload, offsets, cs, ce, wb, sink);
+  const uint32_t c = __reduce_add_sync(0xFFFFFFFFu, sink.collisions);
+  if ((threadIdx.x & 31) == 0 && c) atomicAdd(&T.counters[C_COLLISION], (unsigned long long)c);
 }
 
 // =========================================================================================
@@ -1562,7 +1651,7 @@ __global__ void k_close_release(const __grid_constant__ DevTables T, uint64_t wi
     const uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x, step = (uint64_t)gridDim.x * blockDim.x;
     for (uint64_t r = i; r < T.ring; r += step) T.ring_win[r] = kNoWindow;
     if (!reset) return;
-    if (i < 8) T.counters[i] = 0;
+    if (i < (uint64_t)kCounterSlots) T.counters[i] = 0;
     if (T.part_lg) for (uint64_t q = i; q < ((uint64_t)T.part_ctas << T.part_lg); q += step) T.part_fill[q] = 0;
     return;
   }
@@ -1579,7 +1668,8 @@ cudaError_t configure_kernels(const LaunchGeom& G) {
                        (const void*)k_process_raw<false, false, 0>, (const void*)k_process_raw<false, true, 0>,
                        (const void*)k_process_raw<true, false, 1>, (const void*)k_process_raw<true, false, 2>,
                        (const void*)k_decode<false>, (const void*)k_decode<true>, (const void*)k_process_columns,
-                       (const void*)k_part_drain<true>, (const void*)k_part_drain<false>};
+                       (const void*)k_part_drain<true>, (const void*)k_part_drain<false>,
+                       (const void*)k_verify_keys<false>, (const void*)k_verify_keys<true>};
   for (const void* f : fns) {
     cudaFuncAttributes at;
     cudaError_t e = cudaFuncGetAttributes(&at, f);
@@ -1644,6 +1734,21 @@ cudaError_t launch_decode(const DevSchema& S, const LaunchGeom& G, const uint8_t
   chunk = (chunk + 31u) & ~31u;
   if (S.big_messages) k_decode<true><<<grid, kRawThreads, smem, st>>>(S, payload, offsets, n, chunk, kh, val, status, outcome);
   else k_decode<false><<<grid, kRawThreads, smem, st>>>(S, payload, offsets, n, chunk, kh, val, status, outcome);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_verify_keys(const DevSchema& S, const DevTables& T, const LaunchGeom& G, const uint8_t* payload,
+                               const uint32_t* offsets, uint32_t n, cudaStream_t st, int big_override) {
+  if (n == 0 || !T.dict) return cudaSuccess;
+  size_t smem = (size_t)(kRawThreads / 32) * kWarpBufAlloc + kWarpBufSlack;
+  uint32_t grid = (uint32_t)G.sms;
+  uint32_t need = (n + kRawThreads - 1) / kRawThreads;
+  if (need < grid) grid = need;
+  uint32_t chunk = (n + grid - 1) / grid;
+  chunk = (chunk + 31u) & ~31u;
+  const bool big = big_override < 0 ? S.big_messages != 0 : big_override != 0;
+  if (big) k_verify_keys<true><<<grid, kRawThreads, smem, st>>>(S, T, payload, offsets, n, chunk);
+  else k_verify_keys<false><<<grid, kRawThreads, smem, st>>>(S, T, payload, offsets, n, chunk);
   return cudaGetLastError();
 }
 
@@ -1780,7 +1885,9 @@ cudaError_t launch_init_tables(const DevTables& T, cudaStream_t st) {
   if (T.hist && (e = cudaMemsetAsync(T.hist, 0, rows * T.hist_buckets * 4, st)) != cudaSuccess) return e;
   if ((e = cudaMemsetAsync(T.ring_win, 0xFF, (size_t)T.ring * 8, st)) != cudaSuccess) return e;
   if (T.part_lg && (e = cudaMemsetAsync(T.part_fill, 0, ((size_t)T.part_ctas << T.part_lg) * 4, st)) != cudaSuccess) return e;   // logged tuples are dropped with the tables
-  return cudaMemsetAsync(T.counters, 0, 8 * 8, st);
+  if (T.dict && (e = cudaMemsetAsync(T.dict, 0xFF, T.dict_cap * sizeof(DictEntry), st)) != cudaSuccess) return e;
+  if (T.dict && (e = cudaMemset2DAsync(&T.dict[0].ready, sizeof(DictEntry), 0, 4, T.dict_cap, st)) != cudaSuccess) return e;
+  return cudaMemsetAsync(T.counters, 0, kCounterSlots * 8, st);
 }
 
 }  // namespace bh

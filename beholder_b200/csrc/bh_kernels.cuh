@@ -18,6 +18,9 @@ cudaError_t launch_process_raw(const DevSchema& S, const DevTables& T, const Lau
                                const uint8_t* payload, const uint32_t* offsets, const uint64_t* ts,
                                uint32_t n, cudaStream_t st, int* launches, int big_override = -1);
 // big_override: -1 = follow the schema's message-size hint, 0 / 1 = small / large message kernels
+// BH_F_VERIFY_KEYS: the key bytes of every event of the batch against the dictionary T.dict (no-op without one)
+cudaError_t launch_verify_keys(const DevSchema& S, const DevTables& T, const LaunchGeom& G, const uint8_t* payload,
+                               const uint32_t* offsets, uint32_t n, cudaStream_t st, int big_override = -1);
 // aggregate pre-decoded columns
 cudaError_t launch_process_columns(const DevSchema& S, const DevTables& T, const LaunchGeom& G,
                                    const uint64_t* kh, const uint64_t* ts, const double* val,

@@ -43,7 +43,8 @@ class Aggregator:
                  hist_buckets: int = 64, hist_e0: int = DEFAULT_HIST_E0, hash_seed: int = 0xBE401DE5,
                  device: int = 0, slab_bytes: int = 0, slab_events: int = 0, n_slabs: int = 0,
                  enum_drop: bool = True, message_bytes_hint: int = 0, generic_kernels: bool = False,
-                 max_batch_latency_ms: int = 0, flags: int = 0, part_region_tuples: int = 0, _handle=None):
+                 max_batch_latency_ms: int = 0, flags: int = 0, part_region_tuples: int = 0, verify_keys: bool = False,
+                 debug_hash_mask: int = 0, _handle=None):
         schema = schema or telemetry_progress()
         if mode == L.MODE_WINDOWED:
             schema = schema.with_roles(key=key)
@@ -63,7 +64,8 @@ class Aggregator:
         cfg.slab_events = slab_events
         cfg.n_slabs = n_slabs
         cfg.message_bytes_hint = message_bytes_hint
-        cfg.flags = (L.F_GENERIC_KERNELS if generic_kernels else 0) | flags
+        cfg.flags = (L.F_GENERIC_KERNELS if generic_kernels else 0) | (L.F_VERIFY_KEYS if verify_keys else 0) | flags
+        cfg.debug_hash_mask = debug_hash_mask
         cfg.max_batch_latency_ms = max_batch_latency_ms
         cfg.part_region_tuples = part_region_tuples
         self._commit_cb = None

@@ -28,7 +28,8 @@ typedef enum {
   BH_ERR_TABLE_FULL = -5,    /* a window's key table overflowed: events were dropped */
   BH_ERR_WINDOW_RING = -6,   /* more simultaneously open windows than window_ring */
   BH_ERR_TOO_LARGE = -7,     /* batch exceeds a u32 offset / slab limit */
-  BH_ERR_UNSUPPORTED = -8    /* schema uses a field number or type the kernels do not take */
+  BH_ERR_UNSUPPORTED = -8,   /* schema uses a field number or type the kernels do not take */
+  BH_ERR_KEY_COLLISION = -9  /* BH_F_VERIFY_KEYS: two different keys share a 64-bit hash; their rows are merged */
 } bh_status;
 
 /* declared scalar type of a known field = the protobufjs reader call the generated
@@ -89,6 +90,7 @@ typedef struct bh_config {
                                 * latency of index.js:151,154 under the prefetch limit of index.js:43. */
   uint32_t part_region_tuples; /* partitioned aggregation (BH_F_PARTITIONED): 16-byte tuples per (SM, partition) log
                                 * region; 0 -> 512.  The log takes SMs x partitions x this x 16 bytes of HBM. */
+  uint64_t debug_hash_mask;    /* test hook: key hashes are ANDed with this (0 -> all ones) so that collisions can be made */
 } bh_config;
 #define BH_NO_BATCH_DEADLINE 0xFFFFFFFFu
 
@@ -106,6 +108,14 @@ enum {
                                 * one context must be issued on one stream at a time (the library re-orders itself
                                 * across a change of stream), and reads (snapshot, export, counters) fold the log first. */
   BH_F_NO_PARTITION = 8,
+  BH_F_VERIFY_KEYS = 16,       /* Full-key identity (collisions are detected, never silently merged).
+                                * Rows are identified by the 64-bit hash of their key; with this flag every raw batch is
+                                * also run through a check kernel that keeps, per hash, the key bytes first seen with it
+                                * (a dictionary of 2 x table_capacity entries in HBM) and compares every later event's
+                                * key against them.  A mismatch is counted in bh_counters.key_collisions and bh_flush
+                                * returns BH_ERR_KEY_COLLISION.  Costs a second decode pass; keys must be one string field
+                                * (<= 48 bytes) optionally followed by the status.  Not available for bh_push_columns
+                                * (no key bytes there). */
   BH_F_NO_NUMA_BIND = 2        /* by default the pinned ingest ring (and bh_host_alloc buffers) are allocated while the
                                 * calling thread is confined to the CPUs of the GPU's NUMA node, and the thread's
                                 * affinity is restored afterwards; this flag (or BEHOLDER_NO_NUMA_BIND=1) turns it off */
@@ -127,6 +137,7 @@ typedef struct bh_counters {
   uint64_t dropped_window;     /* -> BH_ERR_WINDOW_RING */
   uint64_t smem_spills;        /* events that bypassed the shared-memory table (diagnostic) */
   uint64_t slow_decodes;       // messages that left the decoder's straight path (diagnostic)
+  uint64_t key_collisions;     /* BH_F_VERIFY_KEYS: events whose key bytes differ from the key first seen with their hash */
 } bh_counters;
 
 typedef struct bh_ctx bh_ctx;
