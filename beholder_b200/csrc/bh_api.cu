@@ -173,7 +173,7 @@ int build_schema(const bh_config& cfg, DevSchema& S) {
   S.hash_seed = cfg.hash_seed;
   S.hash_mask = cfg.debug_hash_mask ? cfg.debug_hash_mask : ~0ull;
   S.has_window = cfg.mode == BH_MODE_WINDOWED && cfg.window_ms > 0;
-  if (S.has_window) S.wdiv = make_div64(cfg.window_ms);
+  if (S.has_window) { S.wdiv = make_div64(cfg.window_ms); S.window_ms = cfg.window_ms; }
   return BH_OK;
 }
 

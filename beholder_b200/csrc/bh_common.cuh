@@ -123,6 +123,7 @@ struct DevSchema {
   int32_t hist_e0;
   uint64_t hash_seed;
   uint64_t hash_mask;     // ANDed onto every key hash (all ones unless the debug_hash_mask test hook is set)
+  uint64_t window_ms;     // the divisor behind wdiv (0 = no windows)
   uint32_t has_window;
   uint32_t int_values;    // the VALUE field is int32 / sint32 / bool (or absent): integer shared-memory table
   // fields the fast decoder recognises by number (0xFFFFFFFF = not applicable)

@@ -163,20 +163,25 @@ __device__ __noinline__ int smem_insert(const SmemTable M, const DevTables& T, u
 
 // Hot half: read-only look-up (plain shared loads, no atomics, no waiting).
 template <bool INTV, bool PART_OK>
+// Called by every lane of `mask` together (there is a warp barrier inside); `eligible` = this lane's event may
+// use the shared table at all.
 __device__ __forceinline__ int smem_find_or_insert(const SmemTable& M, const DevTables& T, uint64_t kh,
-                                                   uint32_t wrel, uint64_t win) {
+                                                   uint32_t wrel, uint64_t win, uint32_t mask, bool eligible) {
   const uint32_t x = (uint32_t)kh ^ (uint32_t)(kh >> 32) ^ (wrel * 0x85EBCA6Bu);
   uint32_t slot = (x * 0x9E3779B1u) >> M.shift;
-  const uint32_t tag = smem_tag(kh, wrel), mask = M.ns - 1;
+  const uint32_t tag = smem_tag(kh, wrel), smask = M.ns - 1;
   const uint32_t* tags = M.tag();
-  uint32_t t = tags[slot];
+  uint32_t t = eligible ? tags[slot] : tag;
   int left = PART_OK && T.part_lg ? kSmemProbesPart : kSmemProbes;
 #pragma unroll 1
-  while (t != tag && t != kTagEmpty) {
-    if (--left == 0) return -1;
-    slot = (slot + 1) & mask;
+  while (t != tag && t != kTagEmpty && --left != 0) {
+    slot = (slot + 1) & smask;
     t = tags[slot];
   }
+  // one exit, and the lanes that left the loop at different iterations are brought together again before the
+  // key compare (measured: that compare ran with 3 of 32 lanes active, once per group of lanes)
+  __syncwarp(mask);
+  if (!eligible || left == 0) return -1;
   if (t == tag && M.key()[slot] == kh) return (int)slot;
   // empty slot, key not stored yet, or another key with the same tag: the out-of-line half sorts it out
   return smem_insert<INTV>(M, T, kh, tag, win, slot, left);
@@ -232,9 +237,8 @@ __device__ __forceinline__ void aggregate_event(const DevSchema& S, const DevTab
                                                 LaneCounters& C, uint32_t mask) {
   const uint32_t ops = S.ops;
   const uint64_t wr = win - wbase;
-  int slot = -1;
-  if (kh < kLockKey && wr < 255ull) slot = smem_find_or_insert<INTV, PART_OK>(M, T, kh, (uint32_t)wr, win);
-  __syncwarp(mask);   // lanes leave the probe loop at different iterations: bring them back before the updates
+  const int slot = smem_find_or_insert<INTV, PART_OK>(M, T, kh, (uint32_t)wr, win, mask, kh < kLockKey && wr < 255ull);
+  __syncwarp(mask);   // (the insert path is divergent) bring the lanes back before the updates
   if (slot >= 0) {
     if (ops & BH_OP_HIST) {
       if (INTV) v = (double)iv;
@@ -650,9 +654,9 @@ struct ProgressSchemaT {
   static constexpr uint32_t fast_value_f64 = 0, tag_key0 = REF ? 0xFFFFFFFFu : 0x0Au, tag_status = 0x10, tag_value = 0x18;
   static constexpr uint32_t skip_str_mask = REF ? ((1u << 1) | (1u << 4)) : (1u << 4), skip_unk_mask = 0xFFFFu & ~0x1Eu;
   // run-time items
-  uint32_t ops; uint64_t enum_mask, hash_seed, hash_mask; Div64 wdiv;
+  uint32_t ops; uint64_t enum_mask, hash_seed, hash_mask, window_ms; Div64 wdiv;
   __device__ __forceinline__ explicit ProgressSchemaT(const DevSchema& S)
-      : dyn(S), ops(S.ops), enum_mask(S.enum_mask), hash_seed(S.hash_seed), hash_mask(S.hash_mask), wdiv(S.wdiv) {}
+      : dyn(S), ops(S.ops), enum_mask(S.enum_mask), hash_seed(S.hash_seed), hash_mask(S.hash_mask), window_ms(S.window_ms), wdiv(S.wdiv) {}
 };
 typedef ProgressSchemaT<false> ProgressSchema;
 
@@ -915,6 +919,20 @@ __device__ __forceinline__ bool decode_block(const SC& S, const SmemRd& r, uint3
   if (!key_is_string) { kh = (uint64_t)status; return true; }            // reference mode: the key is the status itself
   // key hash (bh_common.cuh): 8-byte words of the key bytes, then the length word, then the status word
   uint64_t h = S.hash_seed ^ kHashInit;
+  if (klen == 36u) {                                         // a UUID string: no loop, no masks
+    uint32_t w[10];
+    w[0] = w0;
+#pragma unroll
+    for (int j = 1; j < 10; j++) w[j] = lds32(m + 4u * j);
+#pragma unroll
+    for (int j = 0; j < 4; j++)
+      h = absorb(h, ((uint64_t)__funnelshift_r(w[2 * j + 1], w[2 * j + 2], 16) << 32) | __funnelshift_r(w[2 * j], w[2 * j + 1], 16));
+    h = absorb(h, (uint64_t)__funnelshift_r(w[8], w[9], 16));          // bytes 34..37: the last four key bytes
+    h = absorb(h, len_word(36u, S.part_fld(0)));
+    if (S.n_parts == 2) h = absorb(h, varint_word(status, S.part_fld(1)));
+    kh = fmix64(h) & S.hash_mask;
+    return true;
+  }
   uint32_t wa = w0, a = m + 4u, i = 0;
 #pragma unroll 1
   for (; i + 8u <= klen; i += 8u) {
@@ -1128,7 +1146,14 @@ struct AggSink {
     const uint32_t mask = __ballot_sync(0xFFFFFFFFu, ok);
     if (!ok) return;
     uint64_t win = 0;
-    if (S.has_window) win = div64(ts_ms, S.wdiv);
+    if (S.has_window) {
+      // A CTA's events sit in a few consecutive windows from wbase on: the window is then three 32-bit compares on
+      // the distance from wbase's start instead of a 64-bit division (any other timestamp takes the division).
+      const uint64_t d = ts_ms - wbase * S.window_ms;
+      const uint32_t W = (uint32_t)S.window_ms, lo = (uint32_t)d;
+      if (S.window_ms < (1ull << 30) && d < 4ull * W) win = wbase + ((lo >= W) + (lo >= 2u * W) + (lo >= 3u * W));
+      else win = div64(ts_ms, S.wdiv);
+    }
     aggregate_event<INTV>(S, T, M, kh, win, wbase, value, ival, C, mask);
   }
 };
