@@ -124,6 +124,9 @@ struct DevSchema {
   uint64_t hash_seed;
   uint64_t hash_mask;     // ANDed onto every key hash (all ones unless the debug_hash_mask test hook is set)
   uint64_t window_ms;     // the divisor behind wdiv (0 = no windows)
+  // byte offsets a message of THIS launch may occupy (set per launch): offsets outside are treated as a message
+  // that does not decode, and nothing outside is read, whatever the offsets table says
+  uint32_t pay_lo, pay_hi;
   uint32_t has_window;
   uint32_t int_values;    // the VALUE field is int32 / sint32 / bool (or absent): integer shared-memory table
   // fields the fast decoder recognises by number (0xFFFFFFFF = not applicable)

@@ -654,9 +654,10 @@ struct ProgressSchemaT {
   static constexpr uint32_t fast_value_f64 = 0, tag_key0 = REF ? 0xFFFFFFFFu : 0x0Au, tag_status = 0x10, tag_value = 0x18;
   static constexpr uint32_t skip_str_mask = REF ? ((1u << 1) | (1u << 4)) : (1u << 4), skip_unk_mask = 0xFFFFu & ~0x1Eu;
   // run-time items
-  uint32_t ops; uint64_t enum_mask, hash_seed, hash_mask, window_ms; Div64 wdiv;
+  uint32_t ops, pay_lo, pay_hi; uint64_t enum_mask, hash_seed, hash_mask, window_ms; Div64 wdiv;
   __device__ __forceinline__ explicit ProgressSchemaT(const DevSchema& S)
-      : dyn(S), ops(S.ops), enum_mask(S.enum_mask), hash_seed(S.hash_seed), hash_mask(S.hash_mask), window_ms(S.window_ms), wdiv(S.wdiv) {}
+      : dyn(S), ops(S.ops), pay_lo(S.pay_lo), pay_hi(S.pay_hi), enum_mask(S.enum_mask), hash_seed(S.hash_seed), hash_mask(S.hash_mask),
+        window_ms(S.window_ms), wdiv(S.wdiv) {}
 };
 typedef ProgressSchemaT<false> ProgressSchema;
 
@@ -1038,8 +1039,8 @@ __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefe
 __device__ __forceinline__ void stage_range(const uint8_t* __restrict__ payload, uint32_t A, uint32_t B, uint32_t wb,
                                             uint32_t lane) {
   const uint4* src = reinterpret_cast<const uint4*>(payload + A);
+  if (B <= A) return;
   const uint32_t nvec = (B - A) >> 4;
-  if (nvec == 0) return;
   // lane l copies chunks l, l+32, ...: 32 chunks = 512 B = 8 blocks of 64, so the skewed destination
   // advances by 512 + 8*4 = 544 bytes per step (a 16-byte chunk never straddles a 64-byte block)
   const uint32_t d0 = skew(wb + (lane << 4));
@@ -1068,7 +1069,7 @@ __device__ __forceinline__ void raw_warp_loop(const SC& S, const uint8_t* __rest
                                               const uint32_t* __restrict__ offsets, uint32_t cs, uint32_t ce,
                                               uint32_t wb, Sink& sink) {
   const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
-  const uint32_t total16 = (offsets[ce] + 15u) & ~15u;   // readable bound of this chunk
+  const uint32_t total16 = min((offsets[ce] + 15u) & ~15u, S.pay_hi);   // readable bound of this chunk
   const uint32_t step = nwarps * 32;
   uint32_t e0 = cs + warp * 32;
   uint32_t n0 = 0, n1 = 0;                                // offsets of the batch about to be processed
@@ -1097,7 +1098,7 @@ __device__ __forceinline__ void raw_warp_loop(const SC& S, const uint8_t* __rest
     // is parsed from global memory, every lane its own message.  BIG = true: a batch may also be staged
     // in 2 parts of 16 messages (up to 144 B each) or 4 parts of 8 (up to 288 B) before falling back to
     // global memory.  Same results either way; the host picks the variant from the message-size hint.
-    const bool sane = !valid || o1 >= o0;
+    const bool sane = !valid || (o1 >= o0 && o0 >= S.pay_lo && o1 <= S.pay_hi);
     uint32_t outcome = BH_EV_DROP_DECODE; uint64_t kh = 0; double value = 0.0; int32_t ival = 0; uint32_t status = 0, kloc = 0;
     uint32_t parts = 0;
 #pragma unroll
@@ -1714,10 +1715,18 @@ static uint32_t pick_smem_slots(bool intv, bool hist, const LaunchGeom& G, size_
   return ns;
 }
 
-cudaError_t launch_process_raw(const DevSchema& S, const DevTables& T0, const LaunchGeom& G,
+static DevSchema with_bounds(const DevSchema& S0, uint32_t lo, uint32_t hi) {
+  DevSchema S = S0;
+  S.pay_lo = lo & ~15u;
+  S.pay_hi = hi > 0xFFFFFFF0u ? 0xFFFFFFF0u : (hi + 15u) & ~15u;
+  return S;
+}
+
+cudaError_t launch_process_raw(const DevSchema& S0, const DevTables& T0, const LaunchGeom& G,
                                const uint8_t* payload, const uint32_t* offsets, const uint64_t* ts,
-                               uint32_t n, cudaStream_t st, int* launches, int big_override) {
+                               uint32_t n, cudaStream_t st, int* launches, int big_override, uint32_t lo, uint32_t hi) {
   if (n == 0) return cudaSuccess;
+  const DevSchema S = with_bounds(S0, lo, hi);
   // reference mode only counts: whatever the declared type of `progress`, the (1 024-thread) integer-table
   // kernel does it; the value the decoder hands over is never used
   const bool hist = (S.ops & BH_OP_HIST) != 0, intv = S.int_values != 0 || S.mode == BH_MODE_REFERENCE;
@@ -1747,10 +1756,11 @@ cudaError_t launch_process_raw(const DevSchema& S, const DevTables& T0, const La
   return cudaGetLastError();
 }
 
-cudaError_t launch_decode(const DevSchema& S, const LaunchGeom& G, const uint8_t* payload,
+cudaError_t launch_decode(const DevSchema& S0, const LaunchGeom& G, const uint8_t* payload,
                           const uint32_t* offsets, uint32_t n, uint64_t* kh, double* val,
                           int32_t* status, uint8_t* outcome, cudaStream_t st) {
   if (n == 0) return cudaSuccess;
+  const DevSchema S = with_bounds(S0, 0u, 0xFFFFFFFFu);
   size_t smem = (size_t)(kRawThreads / 32) * kWarpBufAlloc + kWarpBufSlack;
   uint32_t grid = (uint32_t)G.sms;
   uint32_t need = (n + kRawThreads - 1) / kRawThreads;
@@ -1762,9 +1772,10 @@ cudaError_t launch_decode(const DevSchema& S, const LaunchGeom& G, const uint8_t
   return cudaGetLastError();
 }
 
-cudaError_t launch_verify_keys(const DevSchema& S, const DevTables& T, const LaunchGeom& G, const uint8_t* payload,
-                               const uint32_t* offsets, uint32_t n, cudaStream_t st, int big_override) {
+cudaError_t launch_verify_keys(const DevSchema& S0, const DevTables& T, const LaunchGeom& G, const uint8_t* payload,
+                               const uint32_t* offsets, uint32_t n, cudaStream_t st, int big_override, uint32_t lo, uint32_t hi) {
   if (n == 0 || !T.dict) return cudaSuccess;
+  const DevSchema S = with_bounds(S0, lo, hi);
   size_t smem = (size_t)(kRawThreads / 32) * kWarpBufAlloc + kWarpBufSlack;
   uint32_t grid = (uint32_t)G.sms;
   uint32_t need = (n + kRawThreads - 1) / kRawThreads;

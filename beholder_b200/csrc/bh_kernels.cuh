@@ -16,11 +16,14 @@ bool progress_schema_matches(const DevSchema& S);
 // fused proto.decode + enum check + aggregate over one raw batch (index.js:129-138)
 cudaError_t launch_process_raw(const DevSchema& S, const DevTables& T, const LaunchGeom& G,
                                const uint8_t* payload, const uint32_t* offsets, const uint64_t* ts,
-                               uint32_t n, cudaStream_t st, int* launches, int big_override = -1);
+                               uint32_t n, cudaStream_t st, int* launches, int big_override = -1,
+                               uint32_t lo = 0, uint32_t hi = 0xFFFFFFFFu);
 // big_override: -1 = follow the schema's message-size hint, 0 / 1 = small / large message kernels
+// lo, hi: byte offsets the batch's messages may occupy; the kernel reads nothing outside, whatever the offsets say
 // BH_F_VERIFY_KEYS: the key bytes of every event of the batch against the dictionary T.dict (no-op without one)
 cudaError_t launch_verify_keys(const DevSchema& S, const DevTables& T, const LaunchGeom& G, const uint8_t* payload,
-                               const uint32_t* offsets, uint32_t n, cudaStream_t st, int big_override = -1);
+                               const uint32_t* offsets, uint32_t n, cudaStream_t st, int big_override = -1,
+                               uint32_t lo = 0, uint32_t hi = 0xFFFFFFFFu);
 // aggregate pre-decoded columns
 cudaError_t launch_process_columns(const DevSchema& S, const DevTables& T, const LaunchGeom& G,
                                    const uint64_t* kh, const uint64_t* ts, const double* val,

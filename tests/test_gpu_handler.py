@@ -29,7 +29,8 @@ def test_config1_stub_queue_10k_events():
     assert gpu.dropped() == ref.dropped()
     assert amqp.acked == 10_000 == ref.acks()
     assert all(m.acks == 1 for m in amqp.delivered)
-    assert len(side) == 10_000
+    # the side effects of index.js:140-148 run exactly for the messages the reference counted (decoded, named status)
+    assert len(side) == sum(ref.counts().values()) < 10_000
     assert sorted(gpu.progress_updates_total.metrics().splitlines()) == sorted(ref.metrics_text().splitlines())
     vals = {v["labels"]["status"]: v["value"] for v in gpu.progress_updates_total.get()["values"]}
     assert vals == ref.counts()
