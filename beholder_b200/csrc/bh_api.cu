@@ -498,7 +498,12 @@ int bh_create(const bh_config* cfg, bh_ctx** out) {
   if (part) {
     uint32_t lg = 0;
     while ((1ull << lg) < cap) lg++;
-    lg = lg > 22 ? 12 : (lg < 16 ? 6 : lg - 10);                 // ~1024 table slots per partition, 64 .. 4096 partitions
+    // ~2048 table slots per partition, 64 .. 4096 partitions.  Measured at the C3 shape (2^21 slots): 512 / 1024 /
+    // 2048 / 4096 partitions -> 164 / 152 / 159 / 178 DRAM bytes per event (log + fold) and 15.5 / 12.9 / 13.2 /
+    // 16.0 ms per 200 M events: more partitions widen the front of half-written log sectors that L2 has to keep,
+    // fewer crowd the fold's shared table.
+    lg = lg > 23 ? 12 : (lg < 17 ? 6 : lg - 11);
+    if (const char* e = getenv("BEHOLDER_PART_LG")) { int v = atoi(e); if (v >= 4 && v <= 14) lg = (uint32_t)v; }   // experiments
     while ((1u << lg) < ring) lg++;                              // a tuple carries its ring slot in the partition bits
     T.part_lg = lg;
     T.part_cap = cfg->part_region_tuples ? cfg->part_region_tuples : 512;

@@ -1019,10 +1019,19 @@ __device__ __forceinline__ uint32_t warp_buffer_origin(uint32_t first) {
 constexpr int kRawThreads = 1024;      // decode-only kernel and the integer-table fused kernel
 constexpr int kRawThreadsF64 = 768;    // fused kernel with the (larger) f64 table: fewer warp buffers, 4096 slots still fit
 
-// streaming 128-bit load; NOT volatile so that the loads of one batch are issued back to back
+// streaming 128-bit load; NOT volatile so that the loads of one batch are issued back to back.  The payload is
+// read once: its lines are marked evict-first in L2 so that 950 MB of input per launch do not push out what is
+// re-used there -- the HBM table lines and, in partitioned mode, the half-written sectors at the ends of the
+// tuple-log regions (measured at the C3 shape: see DESIGN).
+__device__ __forceinline__ unsigned long long l2_evict_first_policy() {
+  unsigned long long pol;
+  asm("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+  return pol;
+}
 __device__ __forceinline__ uint4 ldg_stream(const uint4* p) {
   uint4 v;
-  asm("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+  const unsigned long long pol = l2_evict_first_policy();
+  asm("ld.global.nc.L1::no_allocate.L2::cache_hint.v4.u32 {%0,%1,%2,%3}, [%4], %5;" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p), "l"(pol));
   return v;
 }
 // the same load pinned to its place in the instruction stream (software pipelining: a plain asm may be sunk to its
