@@ -16,6 +16,10 @@
  *   native.snapshot(ctx, windowId, cap) -> Buffer  // bh_snapshot: packed bh_record rows
  *   native.counters(ctx)   -> Buffer               // bh_get_counters
  *   native.destroy(ctx)
+ *   const g = native.createGroup(localCfg, ownedCfg, [dev0, dev1, ...], ownerStride)   // bh_create_group
+ *   native.groupLocal(g, r) / native.groupOwned(g, r) -> ctx      // contexts owned by the group: never destroy them
+ *   native.groupCloseWindow(g, windowId)           // bh_group_close_window (0xFFFFFFFFFFFFFFFFn = every open window)
+ *   native.groupSync(g)                            // bh_group_sync
  */
 #include <node_api.h>
 #include <stdint.h>
@@ -229,6 +233,59 @@ static napi_value AmqpFeed(napi_env env, napi_callback_info info) {
   return res;
 }
 
+/* ---- several GPUs from this one process (bh_create_group): index.js:23-48 stays a single process ---- */
+static void finalize_group(napi_env env, void* data, void* hint) { (void)env; (void)hint; bh_group_destroy((bh_group*)data); }
+
+static napi_value CreateGroup(napi_env env, napi_callback_info info) {
+  size_t argc = 4; napi_value argv[4]; void *lc, *oc; size_t ll, ol; uint32_t n = 0; int64_t stride = 0; int devices[64];
+  NAPI_OK(napi_get_cb_info(env, info, &argc, argv, NULL, NULL));
+  NAPI_OK(napi_get_buffer_info(env, argv[0], &lc, &ll));
+  NAPI_OK(napi_get_buffer_info(env, argv[1], &oc, &ol));
+  if (ll != sizeof(bh_config) || ol != sizeof(bh_config)) { napi_throw_error(env, NULL, "config buffers must be sizeof(bh_config) bytes"); return NULL; }
+  NAPI_OK(napi_get_array_length(env, argv[2], &n));
+  if (n == 0 || n > 64) { napi_throw_error(env, NULL, "1..64 devices"); return NULL; }
+  for (uint32_t i = 0; i < n; i++) { napi_value e; int32_t d; NAPI_OK(napi_get_element(env, argv[2], i, &e)); NAPI_OK(napi_get_value_int32(env, e, &d)); devices[i] = d; }
+  NAPI_OK(napi_get_value_int64(env, argv[3], &stride));
+  bh_config lcfg, ocfg; memcpy(&lcfg, lc, sizeof lcfg); memcpy(&ocfg, oc, sizeof ocfg);
+  bh_group* g = NULL;
+  int rc = bh_create_group(&lcfg, &ocfg, devices, n, (uint64_t)stride, &g);
+  if (rc != BH_OK) { napi_throw_error(env, NULL, bh_group_last_error()); return NULL; }
+  napi_value ext;
+  NAPI_OK(napi_create_external(env, g, finalize_group, NULL, &ext));
+  return ext;
+}
+
+static napi_value group_ctx(napi_env env, napi_callback_info info, int owned) {
+  size_t argc = 2; napi_value argv[2]; void* g; uint32_t r = 0;
+  NAPI_OK(napi_get_cb_info(env, info, &argc, argv, NULL, NULL));
+  NAPI_OK(napi_get_value_external(env, argv[0], &g));
+  NAPI_OK(napi_get_value_uint32(env, argv[1], &r));
+  bh_ctx* c = owned ? bh_group_owned((bh_group*)g, r) : bh_group_local((bh_group*)g, r);
+  if (!c) { napi_throw_error(env, NULL, "rank out of range"); return NULL; }
+  napi_value ext;
+  NAPI_OK(napi_create_external(env, c, NULL, NULL, &ext));     /* no finalizer: the group owns the context */
+  return ext;
+}
+static napi_value GroupLocal(napi_env env, napi_callback_info info) { return group_ctx(env, info, 0); }
+static napi_value GroupOwned(napi_env env, napi_callback_info info) { return group_ctx(env, info, 1); }
+
+static napi_value GroupCloseWindow(napi_env env, napi_callback_info info) {
+  size_t argc = 2; napi_value argv[2]; void* g; uint64_t w = 0; bool lossless;
+  NAPI_OK(napi_get_cb_info(env, info, &argc, argv, NULL, NULL));
+  NAPI_OK(napi_get_value_external(env, argv[0], &g));
+  NAPI_OK(napi_get_value_bigint_uint64(env, argv[1], &w, &lossless));
+  if (bh_group_close_window((bh_group*)g, w) != BH_OK) { napi_throw_error(env, NULL, bh_group_last_error()); return NULL; }
+  return NULL;
+}
+
+static napi_value GroupSync(napi_env env, napi_callback_info info) {
+  size_t argc = 1; napi_value argv[1]; void* g;
+  NAPI_OK(napi_get_cb_info(env, info, &argc, argv, NULL, NULL));
+  NAPI_OK(napi_get_value_external(env, argv[0], &g));
+  if (bh_group_sync((bh_group*)g) != BH_OK) { napi_throw_error(env, NULL, bh_group_last_error()); return NULL; }
+  return NULL;
+}
+
 static napi_value Init(napi_env env, napi_value exports) {
   napi_property_descriptor props[] = {
     {"create", NULL, Create, NULL, NULL, NULL, napi_default, NULL},
@@ -239,6 +296,11 @@ static napi_value Init(napi_env env, napi_value exports) {
     {"onCommit", NULL, OnCommit, NULL, NULL, NULL, napi_default, NULL},
     {"snapshot", NULL, Snapshot, NULL, NULL, NULL, napi_default, NULL},
     {"counters", NULL, Counters, NULL, NULL, NULL, napi_default, NULL},
+    {"createGroup", NULL, CreateGroup, NULL, NULL, NULL, napi_default, NULL},
+    {"groupLocal", NULL, GroupLocal, NULL, NULL, NULL, napi_default, NULL},
+    {"groupOwned", NULL, GroupOwned, NULL, NULL, NULL, napi_default, NULL},
+    {"groupCloseWindow", NULL, GroupCloseWindow, NULL, NULL, NULL, napi_default, NULL},
+    {"groupSync", NULL, GroupSync, NULL, NULL, NULL, napi_default, NULL},
     {"amqpCreate", NULL, AmqpCreate, NULL, NULL, NULL, napi_default, NULL},
     {"amqpFeed", NULL, AmqpFeed, NULL, NULL, NULL, napi_default, NULL},
   };
