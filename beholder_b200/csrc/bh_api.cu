@@ -506,7 +506,8 @@ int bh_create(const bh_config* cfg, bh_ctx** out) {
     if (const char* e = getenv("BEHOLDER_PART_LG")) { int v = atoi(e); if (v >= 4 && v <= 14) lg = (uint32_t)v; }   // experiments
     while ((1u << lg) < ring) lg++;                              // a tuple carries its ring slot in the partition bits
     T.part_lg = lg;
-    T.part_cap = cfg->part_region_tuples ? cfg->part_region_tuples : 512;
+    // regions x tuples stays constant: 2^20 tuples per SM = 16 MB, 2.5 GB of log on 148 SMs, ~93 M events per fold
+    T.part_cap = cfg->part_region_tuples ? cfg->part_region_tuples : std::max(128u, (1u << 20) >> lg);
     T.part_ctas = (uint32_t)prop.multiProcessorCount;
     const size_t regions = (size_t)T.part_ctas << lg;
     CUB_(cudaMalloc((void**)&T.part_tuples, regions * T.part_cap * sizeof(uint4)));

@@ -877,7 +877,9 @@ __device__ __noinline__ bool decode_slow(const DevSchema& S, const SmemRd r, uin
 // field values by construction; anything else returns false with nothing decided and takes the tiers below.
 template <class SC>
 __device__ __forceinline__ bool decode_block(const SC& S, const SmemRd& r, uint32_t len, uint64_t& kh, uint32_t& status, uint32_t& uval,
-                                             uint32_t& kloc) {
+                                             double& value, uint32_t& kloc) {
+  // (f64 values were tried here too -- three more word pairs for the 8 value bytes -- and made the f64 kernels
+  // slower, 0.443 -> 0.472 ms fused: they are at 72 registers already)
   if (S.fast_value_f64 || S.tag_status > 0x7Fu || S.tag_value > 0x7Fu || S.identity_key) return false;
   const bool key_is_string = S.tag_key0 <= 0x7Fu;
   if (key_is_string ? !(S.n_parts == 1 || (S.n_parts == 2 && S.fast_status_part == 2)) : !S.status_part) return false;
@@ -906,7 +908,7 @@ __device__ __forceinline__ bool decode_block(const SC& S, const SmemRd& r, uint3
     }
   }
   if ((x & 0x80FF80FFu) != (S.tag_status | (S.tag_value << 16))) return false;
-  status = (x >> 8) & 0x7Fu; uval = x >> 24;
+  status = (x >> 8) & 0x7Fu; uval = x >> 24; value = 0.0;
   d += 4u;
   if (d != len) {                                            // one trailing field that ends the message
     if (d + 2u > len) return false;
@@ -964,10 +966,11 @@ __device__ __forceinline__ uint32_t decode_and_check_smem(const SC& S, const Sme
 #ifndef BH_NO_BLOCK_TIER
   {
     uint32_t st = 0, uv = 0;
-    const bool blk = decode_block(S, r, len, kh, st, uv, kloc);
+    double dv = 0.0;
+    const bool blk = decode_block(S, r, len, kh, st, uv, dv, kloc);
     mask = __ballot_sync(mask, !blk);                      // the lanes that go on to the tiers below, together
     if (blk) {
-      P.status = st; P.uval = uv; P.value = 0.0;
+      P.status = st; P.uval = uv; P.value = dv;
       return finish_event(S, P, value, ival, status);
     }
   }
@@ -1141,6 +1144,8 @@ template <bool INTV, class SC>
 struct AggSink {
   const SC& S; const DevTables& T; const SmemTable& M;
   const uint64_t* ts; uint64_t wbase; LaneCounters& C;
+  uint64_t t_base;     // first millisecond of window `wbase`
+  uint32_t w_ms;       // window_ms when the compare path may be used (it fits 30 bits), else 0
   __device__ __forceinline__ void prefetch(uint32_t e2, uint32_t lane) const {
     if (S.has_window && ts && lane < 2) prefetch_l2(ts + e2 + lane * 16);
   }
@@ -1159,9 +1164,9 @@ struct AggSink {
     if (S.has_window) {
       // A CTA's events sit in a few consecutive windows from wbase on: the window is then three 32-bit compares on
       // the distance from wbase's start instead of a 64-bit division (any other timestamp takes the division).
-      const uint64_t d = ts_ms - wbase * S.window_ms;
-      const uint32_t W = (uint32_t)S.window_ms, lo = (uint32_t)d;
-      if (S.window_ms < (1ull << 30) && d < 4ull * W) win = wbase + ((lo >= W) + (lo >= 2u * W) + (lo >= 3u * W));
+      const uint64_t d = ts_ms - t_base;
+      const uint32_t lo = (uint32_t)d;
+      if (d < 4ull * w_ms) win = wbase + ((lo >= w_ms) + (lo >= 2u * w_ms) + (lo >= 3u * w_ms));   // (never taken when w_ms == 0)
       else win = div64(ts_ms, S.wdiv);
     }
     aggregate_event<INTV>(S, T, M, kh, win, wbase, value, ival, C, mask);
@@ -1174,7 +1179,7 @@ __device__ __forceinline__ void process_chunk(const SC& S, const DevTables& T, c
                                               const uint64_t* __restrict__ ts, uint32_t cs, uint32_t ce, uint32_t wb,
                                               LaneCounters& C, uint64_t& wbase) {
   if (S.has_window) { uint64_t w0 = div64(ts ? ts[cs] : 0ull, S.wdiv); wbase = w0 ? w0 - 1 : 0; }
-  AggSink<INTV, SC> sink{S, T, M, ts, wbase, C};
+  AggSink<INTV, SC> sink{S, T, M, ts, wbase, C, wbase * S.window_ms, S.window_ms < (1ull << 30) ? (uint32_t)S.window_ms : 0u};
   raw_warp_loop<BIG>(S, payload, offsets, cs, ce, wb, sink);
 }
 

@@ -322,17 +322,14 @@ def many_key_slabs(keys, events, rank, device, f64):
     return slabs, first
 
 
-def c3_leg(args, device, stream, peak):
-    """configs[2]: 1 GPU, 1 B events streamed once, 1 M distinct keys, 64-bucket log2 histograms, f64 values.  The
-    whole stream is resident in HBM (76 GB of the 180); tables live in a ring of 4 windows, every window is
-    exported to a device buffer (rows + histograms) and recycled as the watermark passes it."""
+def _c3_pass(events, f64, device, stream):
     import torch
     import beholder_b200 as bh
     from beholder_b200 import _lib as L
-    events, keys, cap = args.c3_events, 1_000_000, 1 << 21
+    keys, cap = 1_000_000, 1 << 21
     ops = L.OP_COUNT | L.OP_SUM | L.OP_MIN | L.OP_MAX | L.OP_HIST
-    slabs, first = many_key_slabs(keys, events, 0, device, True)
-    g = bh.Aggregator(bh.telemetry_progress(L.K_DOUBLE), mode=L.MODE_WINDOWED, ops=ops, window_ms=WINDOW_MS,
+    slabs, first = many_key_slabs(keys, events, 0, device, f64)
+    g = bh.Aggregator(bh.telemetry_progress(L.K_DOUBLE if f64 else L.K_INT32), mode=L.MODE_WINDOWED, ops=ops, window_ms=WINDOW_MS,
                       table_capacity=cap, window_ring=4, device=device)
     rows = torch.zeros(cap + 2, 6, dtype=torch.int64, device="cuda")
     hist = torch.zeros(cap + 2, 64, dtype=torch.int32, device="cuda")
@@ -358,19 +355,32 @@ def c3_leg(args, device, stream, peak):
     assert k["events_ok"] == events and k["dropped_table_full"] == 0 and k["dropped_window"] == 0, k
     assert not g.list_windows()
     nbytes = sum(total + 12 * n for *_, n, total in slabs)
-    out = {"workload": f"C3: {events} events x {PAYLOAD_BYTES} B streamed once, {keys} distinct keys, {WINDOW_MS // 1000} s windows, "
+    g.close()
+    del slabs, rows, hist
+    torch.cuda.empty_cache()
+    return {"value": events / (ms * 1e-3), "ms": ms, "events": events, "windows_closed": closed, "rows_exported": int(exported.item()),
+            "smem_miss_frac": k["smem_spills"] / events, "gbs": nbytes / (ms * 1e-3) / 1e9}
+
+
+def c3_leg(args, device, stream, peak):
+    """configs[2]: 1 GPU, 1 B events streamed once, 1 M distinct keys, 64-bucket log2 histograms, f64 values.  The
+    whole stream is resident in HBM (76 GB of the 180); tables live in a ring of 4 windows, every window is
+    exported to a device buffer (rows + histograms) and recycled as the watermark passes it."""
+    r = _c3_pass(args.c3_events, True, device, stream)
+    out = {"workload": f"C3: {r['events']} events x {PAYLOAD_BYTES} B streamed once, 1000000 distinct keys, {WINDOW_MS // 1000} s windows, "
                        f"count/sum/min/max + 64-bucket log2 histograms, f64 values; window ring 4, each window exported (rows + "
                        f"histograms) to a device buffer and recycled behind the watermark",
-           "value": events / (ms * 1e-3), "unit": UNIT, "ms": ms, "events": events, "keys": keys, "windows_closed": closed,
-           "rows_exported": int(exported.item()), "smem_miss_frac": k["smem_spills"] / events,
-           "roofline": {"bound": "hbm", "kernels": "bh::k_process_raw + bh::k_part_drain + export/close", "achieved": nbytes / (ms * 1e-3) / 1e9,
-                        "peak": peak, "unit": "GB/s", "frac": nbytes / (ms * 1e-3) / 1e9 / peak, "algorithmic_bytes_per_event": BYTES_PER_EVENT,
+           "value": r["value"], "unit": UNIT, "ms": r["ms"], "events": r["events"], "keys": 1_000_000, "windows_closed": r["windows_closed"],
+           "rows_exported": r["rows_exported"], "smem_miss_frac": r["smem_miss_frac"],
+           "roofline": {"bound": "hbm", "kernels": "bh::k_process_raw + bh::k_part_drain + export/close", "achieved": r["gbs"],
+                        "peak": peak, "unit": "GB/s", "frac": r["gbs"] / peak, "algorithmic_bytes_per_event": BYTES_PER_EVENT,
                         "traffic_bytes_per_event": ncu_traffic("c3_dram_bytes_per_event"),
                         "note": "whole pass (decode + log + fold + export + close) against the 76 B/event the input costs; table "
                                 "and log traffic are extra (traffic_bytes_per_event, from ncu)"}}
-    g.close()
-    del slabs
-    torch.cuda.empty_cache()
+    # the same shape with the reference's own int32 `progress` (the schema-specialised fused kernel, integer fold)
+    v = _c3_pass(min(args.c3_events, 200_000_000), False, device, stream)
+    out["variant_int32_progress"] = {"value": v["value"], "unit": UNIT, "ms": v["ms"], "events": v["events"], "frac": v["gbs"] / peak,
+                                     "windows_closed": v["windows_closed"]}
     return out
 
 

@@ -89,7 +89,8 @@ typedef struct bh_config {
                                 * BH_NO_BATCH_DEADLINE -> only when full / bh_submit / bh_flush.  Bounds the ack
                                 * latency of index.js:151,154 under the prefetch limit of index.js:43. */
   uint32_t part_region_tuples; /* partitioned aggregation (BH_F_PARTITIONED): 16-byte tuples per (SM, partition) log
-                                * region; 0 -> 512.  The log takes SMs x partitions x this x 16 bytes of HBM. */
+                                * region; 0 -> 2^20 / partitions.  The log takes SMs x partitions x this x 16 bytes of HBM
+                                * (2.5 GB on a B200 by default). */
   uint64_t debug_hash_mask;    /* test hook: key hashes are ANDed with this (0 -> all ones) so that collisions can be made */
 } bh_config;
 #define BH_NO_BATCH_DEADLINE 0xFFFFFFFFu
