@@ -1113,12 +1113,24 @@ __device__ __forceinline__ void raw_warp_loop(const SC& S, const uint8_t* __rest
     const bool sane = !valid || (o1 >= o0 && o0 >= S.pay_lo && o1 <= S.pay_hi);
     uint32_t outcome = BH_EV_DROP_DECODE; uint64_t kh = 0; double value = 0.0; int32_t ival = 0; uint32_t status = 0, kloc = 0;
     uint32_t parts = 0;
+    if constexpr (!BIG) {                                 // small messages: the batch whole, or not at all
+      const uint32_t A = __shfl_sync(0xFFFFFFFFu, o0, 0) & ~15u;
+      if (__all_sync(0xFFFFFFFFu, !valid || (sane && o0 >= A && (o1 - A) <= kWarpBuf))) {
+        const uint32_t bend = __shfl_sync(0xFFFFFFFFu, o1, min(32u, ce - e0) - 1);
+        stage_range(payload, A, min((bend + 15u) & ~15u, total16), wb, lane);
+        __syncwarp();
+        const uint32_t mask = __ballot_sync(0xFFFFFFFFu, valid);
+        if (valid) { SmemRd r{wb + (o0 - A)}; outcome = decode_and_check_smem(S, r, o1 - o0, kh, value, ival, status, mask, kloc); }
+        __syncwarp();                               // the buffer is rewritten by the next batch
+        parts = 1;
+      }
+    }
 #pragma unroll
-    for (uint32_t g = 32; g >= (BIG ? 8u : 32u) && parts == 0; g >>= 1) {
+    for (uint32_t g = 32; BIG && g >= 8u && parts == 0; g >>= 1) {
       const uint32_t ga = __shfl_sync(0xFFFFFFFFu, o0, lane & ~(g - 1)) & ~15u;
       if (__all_sync(0xFFFFFFFFu, !valid || (sane && o0 >= ga && (o1 - ga) <= kWarpBuf))) parts = 32 / g;
     }
-    if (parts) {
+    if (BIG && parts) {
       const uint32_t g = 32 / parts, cnt = min(32u, ce - e0);
       for (uint32_t q = 0; q * g < cnt; q++) {
         const uint32_t A = __shfl_sync(0xFFFFFFFFu, o0, q * g) & ~15u;
@@ -1131,7 +1143,7 @@ __device__ __forceinline__ void raw_warp_loop(const SC& S, const uint8_t* __rest
         __syncwarp();                               // the buffer is rewritten by the next part / batch
         if (!BIG) break;
       }
-    } else if (valid && sane) {
+    } else if (!parts && valid && sane) {
       EventOut out;
       outcome = decode_and_check_gmem(S, payload + o0, o1 - o0, out);
       kh = out.kh; value = out.value; ival = out.ival; status = out.status; kloc = out.kloc;
