@@ -18,6 +18,7 @@ BH_HIST_MAX = 64
 BH_ALL_WINDOWS = 0xFFFFFFFFFFFFFFFF
 BH_STATIC_EXPORT_MAX_OWNERS = 1024
 BH_NO_BATCH_DEADLINE = 0xFFFFFFFF
+BH_COMPACT_BLOCK = 1 << 16
 
 # bh_status
 BH_OK = 0
@@ -94,6 +95,7 @@ PROTOTYPES = {
     "bh_push": (C.c_int, [C.c_void_p, _u8p, C.c_uint32, C.c_uint64]),
     "bh_push_batch": (C.c_int, [C.c_void_p, _u8p, _u32p, _u64p, C.c_uint32]),
     "bh_push_batch_pinned": (C.c_int, [C.c_void_p, _u8p, _u32p, _u64p, C.c_uint32]),
+    "bh_push_batch_compact": (C.c_int, [C.c_void_p, _u8p, C.c_void_p, _u64p, _u64p, C.c_void_p, C.c_uint32]),
     "bh_push_columns": (C.c_int, [C.c_void_p, _u64p, _u64p, _f64p, C.c_uint64]),
     "bh_flush": (C.c_int, [C.c_void_p, C.POINTER(C.c_uint64)]),
     "bh_poll_committed": (C.c_int, [C.c_void_p, C.POINTER(C.c_uint64)]),

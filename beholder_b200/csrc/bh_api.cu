@@ -37,6 +37,8 @@ struct Slab {
   bool in_flight = false;
   uint64_t seq_end = 0;
   cudaEvent_t copied = nullptr, done = nullptr;
+  // compact sidecars (bh_push_batch_compact), allocated on first use
+  uint16_t* d_len = nullptr; int16_t* d_tsd = nullptr;
 };
 
 }  // namespace
@@ -197,6 +199,9 @@ void slab_free(Slab& s) {
   if (s.d_payload) cudaFree(s.d_payload);
   if (s.d_offsets) cudaFree(s.d_offsets);
   if (s.d_ts) cudaFree(s.d_ts);
+  if (s.d_len) cudaFree(s.d_len);
+  if (s.d_tsd) cudaFree(s.d_tsd);
+
   if (s.copied) cudaEventDestroy(s.copied);
   if (s.done) cudaEventDestroy(s.done);
   s = Slab();
@@ -683,6 +688,53 @@ int bh_push_batch_pinned(bh_ctx* c, const uint8_t* slab, const uint32_t* off, co
     if (rc) return rc;
     c->cur = (c->cur + 1) % (uint32_t)c->slabs.size();
     i = j;
+  }
+  return slab_acquire(c, c->cur);
+}
+
+int bh_push_batch_compact(bh_ctx* c, const uint8_t* slab, const uint16_t* lengths, const uint64_t* boff, const uint64_t* ts_block,
+                          const int16_t* ts_delta, uint32_t n) {
+  if (!c || (n && (!slab || !lengths || !boff))) return fail(c, BH_ERR_INVALID, "null argument");
+  const bool with_ts = c->S.has_window;
+  if (with_ts && n && (!ts_block || !ts_delta)) return fail(c, BH_ERR_INVALID, "ts_block / ts_delta required in windowed mode");
+  constexpr uint32_t B = 1u << BH_COMPACT_BLOCK_LG;
+  if (c->slab_events < B) return fail(c, BH_ERR_INVALID, "bh_push_batch_compact needs slab_events >= %u", B);
+  BH_LOCK(c);
+  DeviceGuard guard(c->device);
+  int rc = submit_current(c);          // keep arrival order: anything staged through bh_push goes first
+  if (rc) return rc;
+  const uint32_t n_blocks = (n + B - 1) / B;
+  uint32_t k = 0;                      // first block of the next chunk
+  while (k < n_blocks) {
+    rc = slab_acquire(c, c->cur);
+    if (rc) return rc;
+    Slab& s = c->slabs[c->cur];
+    // as many whole blocks as the ring slab takes (events and bytes)
+    uint32_t k1 = std::min<uint32_t>(n_blocks, k + std::min<uint32_t>(c->slab_events / B, 64u));
+    while (k1 > k && boff[k1] - boff[k] > c->slab_bytes) k1--;
+    if (k1 == k) return fail(c, BH_ERR_TOO_LARGE, "block %u of %llu bytes exceeds slab_bytes", k, (unsigned long long)(boff[k + 1] - boff[k]));
+    if (boff[k1] < boff[k]) return fail(c, BH_ERR_INVALID, "block_offsets must not decrease (at %u)", k);
+    const uint32_t e0 = k * B, m = std::min<uint64_t>(n, (uint64_t)k1 * B) - e0, nb_blocks = k1 - k;
+    const uint64_t nb = boff[k1] - boff[k];
+    if (!s.d_len) {
+      const size_t E = c->slab_events;
+      CU(c, cudaMalloc((void**)&s.d_len, E * 2 + 16));
+      CU(c, cudaMalloc((void**)&s.d_tsd, E * 2 + 16));
+    }
+    cudaStream_t cs = c->st_copy[c->cur & 1];
+    CU(c, cudaMemcpyAsync(s.d_payload, slab + boff[k], nb, cudaMemcpyHostToDevice, cs));
+    CU(c, cudaMemcpyAsync(s.d_len, lengths + e0, (size_t)m * 2, cudaMemcpyHostToDevice, cs));
+    if (with_ts) CU(c, cudaMemcpyAsync(s.d_tsd, ts_delta + e0, (size_t)m * 2, cudaMemcpyHostToDevice, cs));
+    // the few per-block offsets and base timestamps of this chunk go along as kernel arguments
+    CU(c, launch_expand_compact(s.d_len, (const unsigned long long*)(boff + k), (const unsigned long long*)(with_ts ? ts_block + k : nullptr),
+                                s.d_tsd, m, boff[k], s.d_offsets, with_ts ? (unsigned long long*)s.d_ts : nullptr, cs));
+    (void)nb_blocks;
+    c->pushed += m;
+    // offsets are rebuilt from the lengths on the device; the kernel bounds every read by the nb bytes copied
+    rc = slab_launch(c, s, s.d_payload, m, with_ts, cs, nb, 0);
+    if (rc) return rc;
+    c->cur = (c->cur + 1) % (uint32_t)c->slabs.size();
+    k = k1;
   }
   return slab_acquire(c, c->cur);
 }

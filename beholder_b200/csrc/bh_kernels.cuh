@@ -49,6 +49,10 @@ cudaError_t launch_merge_blocks(const DevSchema& S, const DevTables& T, const bh
                                 uint32_t n_blocks, uint64_t stride, const unsigned long long* counts, cudaStream_t st);
 cudaError_t launch_close_window(const DevTables& T, uint64_t window_id, cudaStream_t st);
 cudaError_t launch_reset_tables(const DevTables& T, cudaStream_t st);
+// bh_compact.cu: u16 lengths + i16 timestamp deltas (+ per-block bases) -> u32 offsets, u64 timestamps
+cudaError_t launch_expand_compact(const uint16_t* lengths, const unsigned long long* block_offsets, const unsigned long long* ts_block,
+                                  const int16_t* ts_delta, uint32_t n, unsigned long long chunk_base, uint32_t* offsets,
+                                  unsigned long long* ts, cudaStream_t st);
 cudaError_t configure_kernels(const LaunchGeom& G);
 cudaError_t launch_init_tables(const DevTables& T, cudaStream_t st);
 

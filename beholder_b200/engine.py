@@ -128,6 +128,12 @@ class Aggregator:
         fn = L.lib.bh_push_batch_pinned if pinned else L.lib.bh_push_batch
         self._ck(fn(self._ctx, _ptr(slab), _ptr(offsets), _ptr(ts_ms), n))
 
+    def push_batch_compact(self, slab, lengths, block_offsets, ts_block=None, ts_delta=None) -> None:
+        """caller-pinned batch with compact sidecars (see compact_sidecars): 68 instead of 76 bytes per 64-byte event
+        over PCIe"""
+        self._ck(L.lib.bh_push_batch_compact(self._ctx, _ptr(slab), _ptr(lengths), _ptr(block_offsets), _ptr(ts_block),
+                                             _ptr(ts_delta), len(lengths)))
+
     def push_columns(self, key_hash, ts_ms, value) -> None:
         self._ck(L.lib.bh_push_columns(self._ctx, _ptr(key_hash), _ptr(ts_ms), _ptr(value), len(key_hash)))
 
@@ -277,6 +283,30 @@ class Aggregator:
             if name is not None:
                 out[name.lower()] = int(r["count"])
         return out
+
+
+def compact_sidecars(offsets: np.ndarray, ts_ms: Optional[np.ndarray] = None):
+    """(lengths u16[n], block_offsets u64[ceil(n / 65536) + 1], ts_block u64[...], ts_delta i16[n]) for
+    bh_push_batch_compact from the u32 offsets (relative to the slab start) and u64 timestamps of a batch.  Raises
+    when a message is longer than 65 535 bytes or a timestamp is further than 32 767 ms from its block's base."""
+    B = L.BH_COMPACT_BLOCK
+    n = len(offsets) - 1
+    lens = np.diff(offsets.astype(np.int64))
+    if n and (lens.min() < 0 or lens.max() > 0xFFFF):
+        raise ValueError("message length outside 0..65535")
+    rel = offsets.astype(np.uint64) - np.uint64(offsets[0])
+    nb = (n + B - 1) // B
+    boff = np.concatenate([rel[0:n:B], rel[n:n + 1]]).astype(np.uint64) if n else np.zeros(1, np.uint64)
+    assert len(boff) == nb + 1
+    if ts_ms is None:
+        return lens.astype(np.uint16), boff, None, None
+    t = ts_ms.astype(np.int64)
+    # base of a block = the middle of its range, so that both ends are within reach of an i16
+    tsb = np.array([(int(t[k * B: (k + 1) * B].min()) + int(t[k * B: (k + 1) * B].max())) // 2 for k in range(nb)], dtype=np.int64)
+    delta = t - np.repeat(tsb, B)[:n]
+    if n and (delta.min() < -32768 or delta.max() > 32767):
+        raise ValueError("a timestamp is further than 32767 ms from its block's base: use push_batch")
+    return lens.astype(np.uint16), boff, tsb.astype(np.uint64), delta.astype(np.int16)
 
 
 class PinnedBuffer:

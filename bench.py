@@ -659,6 +659,17 @@ def main():
             hp, ho, ht = pb.view(np.uint8), ob.view(np.uint32), tb.view(np.uint64)
             torch.from_numpy(hp).copy_(p); torch.from_numpy(ho.view(np.int32)).copy_(o); torch.from_numpy(ht.view(np.int64)).copy_(t_)
             pins.append((pb, ob, tb, hp, ho, ht, n, total))
+        # compact sidecars of the same slabs (u16 lengths, i16 timestamp deltas, one offset + base per 65 536 events):
+        # what the end-to-end leg sends, 68 instead of 76 bytes per event over the link that bounds it
+        from beholder_b200.engine import compact_sidecars
+        cpins = []
+        for _, _, _, hp, ho, ht, n, total in pins:
+            arrs = compact_sidecars(ho, ht)
+            bufs = [bh.PinnedBuffer(a.nbytes + 64) for a in arrs]
+            views = []
+            for b, a in zip(bufs, arrs):
+                v = b.view(a.dtype, count=len(a)); v[:] = a; views.append(v)
+            cpins.append((bufs, views, hp[: total + 16], n, total))
         torch.cuda.synchronize()
         # the ingest roofline: plain pinned-host -> device copies of the first slab (CUDA events).
         # One GPU alone (best of 5); with N > 1 also all N GPUs copying at the same time (5 copies back to
@@ -701,16 +712,21 @@ def main():
             pcie_peak = copy_gbs(5, True)
         del dst
         ing = mk()
-        h2d = sum(total + (n + 1) * 4 + n * 8 for *_, n, total in pins)
+        h2d_plain = sum(total + (n + 1) * 4 + n * 8 for *_, n, total in pins)
+        h2d = sum(total + sum(v.nbytes for v in views) for _, views, _, n, total in cpins)
         ing_owned = ing_ex = None
         if world > 1 and exchange == "member":
             from beholder_b200.dist import MemberExchange
             ing_owned = mk()
             ing_ex = MemberExchange(ing, ing_owned, world, rank, owner_stride=stride, device=local_rank)
 
-        def e2e_step():
-            for _, _, _, hp, ho, ht, n, _ in pins:
-                ing.push_batch(hp, ho, ht, pinned=True)
+        def e2e_step(compact=True):
+            if compact:
+                for _, (hl, hb, htb, htd), hpc, n, _ in cpins:
+                    ing.push_batch_compact(hpc, hl, hb, htb, htd)
+            else:
+                for _, _, _, hp, ho, ht, n, _ in pins:
+                    ing.push_batch(hp, ho, ht, pinned=True)
             ing.flush()
             rows = 0
             if ing_ex is not None:
@@ -742,8 +758,9 @@ def main():
         assert k2["events_ok"] == events * (e2e_steps + 1), k2
         e2e = {"value": world * events * e2e_steps / dt, "unit": UNIT, "h2d_bytes_per_step": h2d,
                "d2h_bytes_per_step": rows * 48 + 8 * 40, "steps": e2e_steps,
-               "path": "bh_push_batch_pinned -> (pinned host -> HBM in 64 MiB ring slabs on 2 copy streams) -> "
-                       "k_process_raw -> bh_flush -> " + ("window close to the key owners over NVLink -> bh_snapshot of the owned windows"
+               "bytes_per_event_on_the_link": h2d / events,
+               "path": "bh_push_batch_compact (u16 lengths + i16 timestamp deltas rebuilt on the GPU) -> (pinned host -> HBM in "
+                       "64 MiB ring slabs on 2 copy streams) -> k_process_raw -> bh_flush -> " + ("window close to the key owners over NVLink -> bh_snapshot of the owned windows"
                                                           if ing_ex is not None else "bh_snapshot of every window"),
                "pcie_gbs": world * h2d * e2e_steps / dt / 1e9,
                "pcie_peak_gbs_per_gpu": pcie_peak}
@@ -759,6 +776,15 @@ def main():
         if ing_ex is not None:
             ing_ex.close(); ing_owned.close()
         if world == 1:
+            variants0 = {}
+            e2e_step(False)
+            t0 = time.perf_counter()
+            for _ in range(2):
+                e2e_step(False)
+            d = (time.perf_counter() - t0) / 2
+            variants0["pinned_u32_offsets_u64_ts"] = {"value": events / d, "unit": UNIT, "pcie_gbs": h2d_plain / d / 1e9, "pcie_frac": h2d_plain / d / 1e9 / pcie_peak,
+                                                      "bytes_per_event_on_the_link": h2d_plain / events,
+                                                      "path": "bh_push_batch_pinned (round 1's e2e path: u32 offsets + u64 timestamps travel with the payload)"}
             # the drop-in ingest paths: what a Node Buffer goes through.  (a) bh_push_batch from ordinary (pageable)
             # host memory: the library copies into its pinned ring first; (b) bh_push, one call per message, as
             # addon/beholder_napi.c does for each rmsg.message.content (index.js:129) -- driven from C so that no
@@ -766,7 +792,7 @@ def main():
             hp0, ho0, ht0, n0, total0 = pins[0][3], pins[0][4], pins[0][5], pins[0][6], pins[0][7]
             pg = (np.array(hp0, copy=True), np.array(ho0, copy=True), np.array(ht0, copy=True))     # pageable copies
             b0 = total0 + (n0 + 1) * 4 + n0 * 8
-            variants = {}
+            variants = variants0
             for name, fn in (("pageable_batch", lambda: ing.push_batch(*pg)),
                              ("per_message_push", lambda: L.check(L.lib.bh_debug_push_each(ing._ctx, pg[0].ctypes.data, pg[1].ctypes.data,
                                                                                           pg[2].ctypes.data, n0), ing._ctx))):
@@ -804,6 +830,9 @@ def main():
         ing.close()
         for pb, ob, tb, *_ in pins:
             pb.free(); ob.free(); tb.free()
+        for bufs, *_ in cpins:
+            for b in bufs:
+                b.free()
 
     if rank == 0:
         peak, peak_src = peaks()

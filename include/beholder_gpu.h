@@ -159,6 +159,18 @@ int bh_push_batch(bh_ctx* ctx, const uint8_t* slab, const uint32_t* offsets, con
 /* same, but slab/offsets/ts_ms are in pinned host memory (bh_host_alloc) and stay valid until
  * committed: copied to the device straight from the caller's buffers. */
 int bh_push_batch_pinned(bh_ctx* ctx, const uint8_t* slab, const uint32_t* offsets, const uint64_t* ts_ms, uint32_t n);
+/* bh_push_batch_pinned with compact sidecars.  End to end the path is bound by the PCIe link, so what
+ * travels with each message matters: a u16 LENGTH and an i16 timestamp DELTA instead of a u32 offset and a u64
+ * timestamp take a 64-byte event from 76 to 68 bytes on the link; the offsets and timestamps are rebuilt on the
+ * GPU.  Messages lie back to back from `slab` on (caller-pinned memory, as are all arrays; they must stay valid
+ * until committed).  Per block of BH_COMPACT_BLOCK = 65 536 messages the caller gives block_offsets[k] = byte
+ * offset of message k * 65 536 from `slab` (one extra entry at the end = total bytes) and ts_block[k] = a base
+ * timestamp; ts_ms of message i = ts_block[i >> 16] + ts_delta[i].  A message longer than 65 535 bytes or a
+ * timestamp further than +-32 767 ms from its block's base does not fit: use bh_push_batch_pinned for such a batch.
+ * ts_block / ts_delta may be NULL where timestamps are not used.  slab_events must be at least 65 536. */
+#define BH_COMPACT_BLOCK_LG 16
+int bh_push_batch_compact(bh_ctx* ctx, const uint8_t* slab, const uint16_t* lengths, const uint64_t* block_offsets,
+                          const uint64_t* ts_block, const int16_t* ts_delta, uint32_t n);
 /* pre-decoded columns (the counter side alone: metrics.progress_updates_total.inc, index.js:136-138) */
 int bh_push_columns(bh_ctx* ctx, const uint64_t* key_hash, const uint64_t* ts_ms, const double* value, uint64_t n);
 /* submit the partial slab and wait until everything pushed so far is aggregated */
