@@ -7,15 +7,20 @@
 Workload (BASELINE.json configs[1], "C2"): per GPU 100 M synthetic api.TelemetryProgress events of
 64 B, 1 000 distinct (mediaId, status) keys, 10 s tumbling windows, count/sum/min/max.  A step is one
 pass of the fused decode+aggregate kernel over those events (8 slabs of 12.5 M events = 8 launches),
-plus, at N > 1, the window-close exchange (export by owner straight into the owners' buffers over NVLink, or -> NCCL all-to-all; -> merge).
+plus, at N > 1, the window-close exchange of the library (bh_member_close_window: rows stored straight into the key
+owners' buffers over NVLink, flag barrier in peer memory, merge; NCCL all-to-all as the fallback).
 
 `value`  : events/s, inputs resident in HBM, CUDA-event timed, max over ranks.
-`e2e`    : events/s through the C-ABI ingest (bh_push_batch_pinned -> bh_flush -> bh_snapshot): pinned
-           HOST buffers, H2D copies and the D2H read of the result inside the timed region.
+`e2e`    : events/s through the C-ABI ingest (bh_push_batch_compact -> bh_flush -> window close at N > 1 ->
+           bh_snapshot): pinned HOST buffers, H2D copies and the D2H read of the result inside the timed region;
+           `e2e.variants` (N = 1): the other ingest paths (u32 offsets + u64 timestamps, pageable memory, one call
+           per message, buffers registered in place).
 `roofline`: fused kernel, algorithmic bytes (payload + 4 B offset + 8 B timestamp per event) over its
            average launch time, against the measured HBM copy bandwidth (MEASURED_PEAKS.json).
 `cpu_baseline`: the CPU oracle (a C restatement of the reference handler; Node and triton-core are
            not available, so kind = "port") on the box's host cores, bounded sample.
+`c3`, `c5` (N = 1), `c4` (N > 1): BASELINE.json configs 3, 5 and 4 as extra keys of the same line.
+`exchange_check` (N > 1): the exchange the timed loop used, against the CPU oracle.
 """
 from __future__ import annotations
 
