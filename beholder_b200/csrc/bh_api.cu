@@ -503,11 +503,12 @@ int bh_create(const bh_config* cfg, bh_ctx** out) {
   if (part) {
     uint32_t lg = 0;
     while ((1ull << lg) < cap) lg++;
-    // ~2048 table slots per partition, 64 .. 4096 partitions.  Measured at the C3 shape (2^21 slots): 512 / 1024 /
+    // ~2048 table slots per partition, 64 .. 2048 partitions (at 2^24 slots 4 096 partitions are 5 % slower than
+    // 1 024 or 2 048: the scatter of the log phase pays for every extra open region).  Measured at the C3 shape (2^21 slots): 512 / 1024 /
     // 2048 / 4096 partitions -> 164 / 152 / 159 / 178 DRAM bytes per event (log + fold) and 15.5 / 12.9 / 13.2 /
     // 16.0 ms per 200 M events: more partitions widen the front of half-written log sectors that L2 has to keep,
     // fewer crowd the fold's shared table.
-    lg = lg > 23 ? 12 : (lg < 17 ? 6 : lg - 11);
+    lg = lg > 22 ? 11 : (lg < 17 ? 6 : lg - 11);
     if (const char* e = getenv("BEHOLDER_PART_LG")) { int v = atoi(e); if (v >= 4 && v <= 14) lg = (uint32_t)v; }   // experiments
     while ((1u << lg) < ring) lg++;                              // a tuple carries its ring slot in the partition bits
     T.part_lg = lg;
