@@ -10,6 +10,8 @@
 //
 // Nothing here is a dense contraction: no tensor cores.  The kernels are bound by HBM bandwidth,
 // by instruction issue (the wire-format walk) or by L2 atomics (large key sets).
+#include <atomic>
+
 #include "bh_kernels.cuh"
 
 namespace bh {
@@ -1884,7 +1886,8 @@ cudaError_t launch_export(const DevSchema& S, const DevTables& T, uint64_t windo
 // for the runtime, not a device address: the address is looked up once per device with
 // cudaGetSymbolAddress (with that device current) and it is that pointer the kernels receive.
 static __device__ __align__(256) unsigned long long g_static_export_cursor[BH_STATIC_EXPORT_MAX_OWNERS];
-static unsigned long long* g_static_export_cursor_addr[64];   // per device ordinal, filled on first use
+static std::atomic<unsigned long long*> g_static_export_cursor_addr[64];   // per device ordinal, filled on first use (two
+                                                                           // threads racing here store the same address)
 
 cudaError_t launch_export_static(const DevSchema& S, const DevTables& T, uint64_t window_id, uint32_t n_owners,
                                  bh_record* out, uint32_t* hist_out, uint64_t cap, uint64_t owner_stride,
@@ -1893,16 +1896,17 @@ cudaError_t launch_export_static(const DevSchema& S, const DevTables& T, uint64_
   cudaError_t e = cudaGetDevice(&dev);
   if (e != cudaSuccess) return e;
   if (dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
-  if (!g_static_export_cursor_addr[dev]) {          // set-up: first call on this device
+  unsigned long long* cursor = g_static_export_cursor_addr[dev].load(std::memory_order_acquire);
+  if (!cursor) {                                    // set-up: first call on this device
     void* p = nullptr;
     e = cudaGetSymbolAddress(&p, g_static_export_cursor);
     if (e != cudaSuccess) return e;
-    g_static_export_cursor_addr[dev] = (unsigned long long*)p;
+    cursor = (unsigned long long*)p;
+    g_static_export_cursor_addr[dev].store(cursor, std::memory_order_release);
   }
   // k_export_prefix rewrites cursor[0 .. n_owners) on every call, so nothing of the previous call's
   // contents is read; owner_counts is zeroed by launch_export (a memset, not an allocation).
-  return launch_export(S, T, window_id, n_owners, out, hist_out, cap, owner_stride, owner_counts,
-                       g_static_export_cursor_addr[dev], st);
+  return launch_export(S, T, window_id, n_owners, out, hist_out, cap, owner_stride, owner_counts, cursor, st);
 }
 
 cudaError_t launch_merge(const DevSchema& S, const DevTables& T, const bh_record* recs,
