@@ -310,30 +310,32 @@ def many_key_pass(local, slabs, stream, on_close):
     return ws.closed
 
 
-def many_key_slabs(keys, events, rank, device, f64):
+def many_key_slabs(keys, events, rank, device, f64, zipf=False):
+    import numpy as np
     import torch
-    from beholder_b200.synth import SynthSpec, generate_device
+    from beholder_b200.synth import SynthSpec, generate_device, zipf_cdf
     spec = SynthSpec(n_keys=keys, rate_per_ms=MANY_RATE, jitter_ms=MANY_JITTER, payload_bytes=PAYLOAD_BYTES, value_f64=f64,
-                     value_exp_lo=-12, value_exp_span=24)
+                     value_exp_lo=-12, value_exp_span=24, zipf=zipf)
+    d_cdf = torch.from_numpy(zipf_cdf(keys).view(np.int64)).to(torch.device("cuda", device)) if zipf else None
     slabs, g = [], 0
     first = rank * events           # ranks take consecutive stretches of the event index space ...
     spec.t0_ms -= first // MANY_RATE  # ... that cover the same stream time (round-robin delivery)
     while g < events:
         n = min(MANY_SLAB, events - g)
-        p, o, t, total = generate_device(spec, first + g, n, device=device)
+        p, o, t, total = generate_device(spec, first + g, n, device=device, d_cdf=d_cdf)
         slabs.append((p[: (total + 15) // 16 * 16 + 16].clone(), o, t, n, total))
         g += n
     torch.cuda.synchronize()
     return slabs, first
 
 
-def _c3_pass(events, f64, device, stream):
+def _c3_pass(events, f64, device, stream, zipf=False):
     import torch
     import beholder_b200 as bh
     from beholder_b200 import _lib as L
     keys, cap = 1_000_000, 1 << 21
     ops = L.OP_COUNT | L.OP_SUM | L.OP_MIN | L.OP_MAX | L.OP_HIST
-    slabs, first = many_key_slabs(keys, events, 0, device, f64)
+    slabs, first = many_key_slabs(keys, events, 0, device, f64, zipf)
     g = bh.Aggregator(bh.telemetry_progress(L.K_DOUBLE if f64 else L.K_INT32), mode=L.MODE_WINDOWED, ops=ops, window_ms=WINDOW_MS,
                       table_capacity=cap, window_ring=4, device=device)
     rows = torch.zeros(cap + 2, 6, dtype=torch.int64, device="cuda")
@@ -386,6 +388,10 @@ def c3_leg(args, device, stream, peak):
     v = _c3_pass(min(args.c3_events, 200_000_000), False, device, stream)
     out["variant_int32_progress"] = {"value": v["value"], "unit": UNIT, "ms": v["ms"], "events": v["events"], "frac": v["gbs"] / peak,
                                      "windows_closed": v["windows_closed"]}
+    # Zipf(1.0) keys (SURVEY 8d asks for both distributions): hot keys stay in the per-SM table, the tail is logged
+    z = _c3_pass(min(args.c3_events, 200_000_000), True, device, stream, zipf=True)
+    out["variant_zipf_keys"] = {"value": z["value"], "unit": UNIT, "ms": z["ms"], "events": z["events"], "frac": z["gbs"] / peak,
+                                "smem_miss_frac": z["smem_miss_frac"], "windows_closed": z["windows_closed"]}
     return out
 
 
@@ -457,13 +463,29 @@ def c4_leg(args, world, rank, device, stream, peak):
     return out
 
 
-def c5_leg(device, stream, peak, pcie_peak):
-    """configs[4] on this GPU: payload 64 B .. 4 KB, HBM-resident and end to end.  Bytes: `read_bytes` counts what
-    the kernel has to touch -- all of a message while batches are staged through shared memory (<= 288 B), the
-    fields it parses plus the headers it skips once messages are read from global memory (the pad is skipped)."""
+def c5_leg(device, stream, peak, pcie_peak, world=1, rank=0):
+    """configs[4]: payload 64 B .. 4 KB on every GPU of the run at once, HBM-resident and end to end; events/s are
+    summed over the GPUs, fractions are per GPU (HBM) and against `pcie_peak` (the link peak the caller measured:
+    one GPU alone at N = 1, all GPUs copying at once at N > 1).  Bytes: `hbm_read_gbs` counts what the kernel has to
+    touch -- all of a message while batches are staged through shared memory (<= 288 B), the fields it parses plus
+    the headers it skips once messages are read from global memory (the pad is skipped)."""
     import numpy as np
     import torch
+    import torch.distributed as dist
     import beholder_b200 as bh
+
+    def sync_all():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+
+    def summed(v, op="sum"):
+        if world == 1:
+            return v
+        t = torch.tensor([v], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.SUM if op == "sum" else dist.ReduceOp.MAX)
+        return t.item()
+
     from beholder_b200 import _lib as L
     from beholder_b200.synth import SynthSpec, generate_device
     ops = L.OP_COUNT | L.OP_SUM | L.OP_MIN | L.OP_MAX
@@ -471,18 +493,19 @@ def c5_leg(device, stream, peak, pcie_peak):
     for payload in (64, 128, 256, 512, 1024, 2048, 4096):
         n = max(500_000, min(12_500_000, (800 << 20) // payload))
         spec = SynthSpec(n_keys=N_KEYS, rate_per_ms=500, payload_bytes=payload)
-        p, o, t, total = generate_device(spec, 0, n, device=device)
+        p, o, t, total = generate_device(spec, rank * n, n, device=device)
         mk = lambda: bh.Aggregator(mode=L.MODE_WINDOWED, ops=ops, window_ms=WINDOW_MS, table_capacity=2048, window_ring=32,  # noqa: E731
                                    device=device, message_bytes_hint=payload, slab_bytes=64 << 20, slab_events=1 << 20, n_slabs=4)
         g = mk()
         for _ in range(3):
             g.process_device(p, o, t, n, stream=stream)
+        sync_all()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         for _ in range(5):
             g.process_device(p, o, t, n, stream=stream)
         e1.record(); torch.cuda.synchronize()
-        ms = e0.elapsed_time(e1) / 5
+        ms = summed(e0.elapsed_time(e1) / 5, "max")
         g.close()
         staged = payload <= 288
         touched = (total if staged else n * 96) + 12 * n     # global-memory reader: ~64 B of fields + 32 B sectors of the skipped pad's header
@@ -492,16 +515,18 @@ def c5_leg(device, stream, peak, pcie_peak):
         torch.cuda.synchronize()
         g = mk()
         g.push_batch(hp, ho, ht, pinned=True); g.flush()
+        sync_all()
         t0 = time.perf_counter()
         for _ in range(2):
             g.push_batch(hp, ho, ht, pinned=True)
         g.flush()
-        dt = (time.perf_counter() - t0) / 2
+        sync_all()
+        dt = summed((time.perf_counter() - t0) / 2, "max")
         g.close(); pb.free(); ob.free(); tb.free()
         wire = total + 12 * n
-        hbm_frac, pcie_frac = touched / (ms * 1e-3) / 1e9 / peak, wire / dt / 1e9 / pcie_peak
-        out.append({"payload_bytes": payload, "events": n, "hbm_events_per_s": n / (ms * 1e-3), "hbm_read_gbs": touched / (ms * 1e-3) / 1e9,
-                    "hbm_frac": hbm_frac, "e2e_events_per_s": n / dt, "e2e_pcie_gbs": wire / dt / 1e9, "e2e_pcie_frac": pcie_frac,
+        hbm_frac, pcie_frac = touched / (ms * 1e-3) / 1e9 / peak, world * wire / dt / 1e9 / pcie_peak
+        out.append({"payload_bytes": payload, "events_per_gpu": n, "hbm_events_per_s": world * n / (ms * 1e-3), "hbm_read_gbs_per_gpu": touched / (ms * 1e-3) / 1e9,
+                    "hbm_frac": hbm_frac, "e2e_events_per_s": world * n / dt, "e2e_pcie_gbs": world * wire / dt / 1e9, "e2e_pcie_frac": pcie_frac,
                     "regime": "ingest-bound end to end (PCIe); HBM-resident: " +
                               ("instruction issue (decode)" if staged else "latency of per-message global reads (pad skipped, not read)")})
         del p, o, t
@@ -868,6 +893,8 @@ def main():
             line["cpu_baseline"] = cpu_baseline_block(True)
     # ---- BASELINE.json configs 3, 4, 5 (extra keys of the same line; a failure is reported, not fatal) ----
     extra = {}
+    # the N-GPU link peak the c5 leg compares with: known to every rank (rank 0 alone holds `e2e`)
+    pcie_conc_all = (pcie_concurrent if (not args.no_e2e and world > 1 and pcie_concurrent) else 55.0 * world)
     if not args.no_extra:
         local.close(); local = None
         if exch is not None and hasattr(exch, "close"):
@@ -877,7 +904,8 @@ def main():
         peak_gbs = peaks()[0]
         legs = [("c3", lambda: c3_leg(args, local_rank, stream, peak_gbs)),
                 ("c5", lambda: c5_leg(local_rank, stream, peak_gbs, e2e["pcie_peak_gbs_per_gpu"] if e2e else 55.0))] if world == 1 else \
-               [("c4", lambda: c4_leg(args, world, rank, local_rank, stream, peak_gbs))]
+               [("c4", lambda: c4_leg(args, world, rank, local_rank, stream, peak_gbs)),
+                ("c5", lambda: c5_leg(local_rank, stream, peak_gbs, pcie_conc_all, world, rank))]
         # The headline above must never be lost to an extra leg.  One GPU: an exception is recorded in the leg's
         # place.  Several GPUs: a rank that failed would leave its peers waiting in a barrier for ever, so every
         # rank arms a watchdog: past the deadline rank 0 prints the line with the leg marked as timed out and all
