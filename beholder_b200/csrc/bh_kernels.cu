@@ -290,7 +290,11 @@ __device__ __forceinline__ void aggregate_event(const DevSchema& S, const DevTab
 
 // CTA end: every shared entry goes to its HBM slot.  Events of an entry whose window or key cannot
 // be placed move from the "ok" counter to the drop counter that explains them.
-template <bool INTV>
+// PART_OK (the scattering kernels in partitioned mode): an entry that absorbed a single event is that event -- its
+// sum is its value -- so it is logged as a tuple like the events that missed the table, instead of costing a
+// random HBM update now.  With large uniform key sets that is nearly every entry of the table.  (Not with
+// histograms: there the entry's HBM slot was claimed and its bucket counted when the event arrived.)
+template <bool INTV, bool PART_OK = false>
 __device__ __forceinline__ void smem_table_flush(const DevSchema& S, const DevTables& T, const SmemTable& M, uint64_t wbase) {
   // every CTA hashes a key to the same shared slot: rotate the scan by CTA so that the CTAs do not all
   // hit the same HBM entry at the same moment (same-address L2 atomics serialise)
@@ -302,6 +306,8 @@ __device__ __forceinline__ void smem_table_flush(const DevSchema& S, const DevTa
     if (k == kEmptyKey || c == 0) continue;
     uint64_t win = wbase + (M.tag()[i] >> 24);
     uint32_t r = (uint32_t)win & (T.ring - 1);
+    if (PART_OK && T.part_lg && !M.hist && c == 1 && k < kLockKey &&
+        part_scatter(T, k, win, (uint64_t)__double_as_longlong(INTV ? (double)M.imin()[i] : M.fsum()[i]))) continue;
     uint32_t gs = M.hist ? M.gslot<INTV>()[i] : g_find_or_insert(T, win, k, &r);
     if (gs >= kGslotWindow) {
       if (!M.hist) {   // (with histograms on, the event was already refused when it arrived)
@@ -1232,7 +1238,7 @@ k_process_raw(const __grid_constant__ DevSchema S, const __grid_constant__ DevTa
     }
   }
   __syncthreads();
-  smem_table_flush<INTV>(S, T, M, wbase);
+  smem_table_flush<INTV, true>(S, T, M, wbase);
   part_cursors_store(T);
   counters_flush(T, C);
 }
@@ -1388,7 +1394,7 @@ k_process_columns(const __grid_constant__ DevSchema S, const __grid_constant__ D
     if (ok) aggregate_event<false>(S, T, M, k, win, wbase, v, 0, C, mask);
   }
   __syncthreads();
-  smem_table_flush<false>(S, T, M, wbase);
+  smem_table_flush<false, true>(S, T, M, wbase);
   part_cursors_store(T);
   counters_flush(T, C);
 }
