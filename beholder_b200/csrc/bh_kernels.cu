@@ -225,7 +225,8 @@ __device__ __forceinline__ void part_cursors_load(const DevTables& T) {
   for (uint32_t i = threadIdx.x; i < (1u << T.part_lg); i += blockDim.x) cur[i] = T.part_fill[((uint64_t)blockIdx.x << T.part_lg) + i];
 }
 __device__ __forceinline__ void part_cursors_store(const DevTables& T) {
-  if (!T.part_lg) return;
+  if (!T.part_lg) return;            // (uniform over the CTA)
+  __syncthreads();                   // the flush just before still appends tuples
   const uint32_t* cur = (const uint32_t*)(g_smem + T.part_smem_off);
   for (uint32_t i = threadIdx.x; i < (1u << T.part_lg); i += blockDim.x) T.part_fill[((uint64_t)blockIdx.x << T.part_lg) + i] = min(cur[i], T.part_cap);
 }
@@ -306,8 +307,14 @@ __device__ __forceinline__ void smem_table_flush(const DevSchema& S, const DevTa
     if (k == kEmptyKey || c == 0) continue;
     uint64_t win = wbase + (M.tag()[i] >> 24);
     uint32_t r = (uint32_t)win & (T.ring - 1);
-    if (PART_OK && T.part_lg && !M.hist && c == 1 && k < kLockKey &&
-        part_scatter(T, k, win, (uint64_t)__double_as_longlong(INTV ? (double)M.imin()[i] : M.fsum()[i]))) continue;
+    if (PART_OK && T.part_lg && !M.hist && c == 1 && k < kLockKey) {
+      // the event's value, from whichever column the configured ops keep (the max/min columns hold its exact
+      // bits, -0.0 included; the sum column holds 0.0 + v)
+      uint64_t vb;
+      if (INTV) vb = (uint64_t)__double_as_longlong((double)((S.ops & BH_OP_SUM) ? (int32_t)M.sum_lo()[i] : (S.ops & BH_OP_MIN) ? M.imin()[i] : (S.ops & BH_OP_MAX) ? M.imax()[i] : 0));
+      else vb = (S.ops & BH_OP_MAX) ? f64_unorder(M.fmax_ord()[i]) : (S.ops & BH_OP_MIN) ? f64_unorder(~M.fmin_inv()[i]) : (uint64_t)__double_as_longlong(M.fsum()[i]);
+      if (part_scatter(T, k, win, vb)) continue;
+    }
     uint32_t gs = M.hist ? M.gslot<INTV>()[i] : g_find_or_insert(T, win, k, &r);
     if (gs >= kGslotWindow) {
       if (!M.hist) {   // (with histograms on, the event was already refused when it arrived)

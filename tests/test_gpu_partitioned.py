@@ -65,6 +65,15 @@ def test_forced_on_a_small_table(zipf, f64):
     assert k["smem_spills"] > (100_000 if zipf else 1_000_000)
 
 
+@pytest.mark.parametrize("f64", [False, True])
+@pytest.mark.parametrize("ops", [L.OP_COUNT, L.OP_COUNT | L.OP_MIN, L.OP_COUNT | L.OP_MAX, L.OP_SUM, L.OP_SUM | L.OP_MIN | L.OP_MAX])
+def test_single_event_entries_logged_at_the_flush_under_every_op_subset(ops, f64):
+    # many keys, few events each, no histograms: most front-table entries end a launch holding ONE event and are
+    # logged as a tuple whose value comes from whichever column the ops keep
+    spec = SynthSpec(n_keys=400_000, rate_per_ms=200, value_f64=f64, value_signed=True)
+    _check(spec, 2, 600_000, ops, 1 << 20, threads=16)
+
+
 def test_partitioning_is_on_by_itself_for_large_tables_and_can_be_kept_off():
     spec = SynthSpec(n_keys=100_000, rate_per_ms=400)
     k_on = _check(spec, 1, 2_000_000, ALL_OPS, 1 << 18, flags=0, threads=16)
