@@ -510,7 +510,13 @@ int bh_create(const bh_config* cfg, bh_ctx** out) {
     // fewer crowd the fold's shared table.
     lg = lg > 22 ? 11 : (lg < 17 ? 6 : lg - 11);
     if (const char* e = getenv("BEHOLDER_PART_LG")) { int v = atoi(e); if (v >= 4 && v <= 14) lg = (uint32_t)v; }   // experiments
-    while ((1u << lg) < ring) lg++;                              // a tuple carries its ring slot in the partition bits
+    // probing wraps inside a partition's slice (g_probe_wrap): keep slices large enough to fill like the table
+    // does (256 slots: +- 8 keys around the mean)
+    uint32_t lgcap = 0;
+    while ((1ull << lgcap) < cap) lgcap++;
+    if (lgcap < lg + 8) lg = lgcap - 8;                          // (cap >= 64 was checked; small forced tables only)
+    if (lgcap < 8 || (1u << lg) < ring || lg < 1)                // a tuple carries its ring slot in the partition bits
+      return fail(nullptr, BH_ERR_INVALID, "BH_F_PARTITIONED needs table_capacity >= 256 x max(2, window_ring) slots");
     T.part_lg = lg;
     // regions x tuples stays constant: 2^20 tuples per SM = 16 MB, 2.5 GB of log on 148 SMs, ~93 M events per fold
     T.part_cap = cfg->part_region_tuples ? cfg->part_region_tuples : std::max(128u, (1u << 20) >> lg);

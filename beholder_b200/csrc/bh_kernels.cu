@@ -24,6 +24,32 @@ constexpr uint32_t kGslotWindow = 0xFFFFFFFEu;
 
 __device__ __forceinline__ uint32_t ilog2_u64(uint64_t v) { return 63u - (uint32_t)__clzll((long long)v); }
 
+// Probe `n` slots of ring slot r's key column for `kh`, starting at `slot`, stepping inside the aligned block of
+// wrap + 1 slots that holds `slot`.  Returns the slot found or claimed, or kGslotFull.
+__device__ __forceinline__ uint32_t g_probe_from(const DevTables& T, uint32_t r, uint64_t kh, uint64_t slot, uint64_t wrap, uint64_t n) {
+  unsigned long long* keys = T.keys + (uint64_t)r * T.stride;
+  const uint64_t hi = slot & ~wrap;
+  for (uint64_t i = 0; i < n; i++) {
+    unsigned long long k = keys[slot];
+    if (k == kh) return (uint32_t)slot;
+    if (k == kEmptyKey) {
+      unsigned long long old = atomicCAS(&keys[slot], (unsigned long long)kEmptyKey, (unsigned long long)kh);
+      if (old == kEmptyKey || old == kh) return (uint32_t)slot;
+    }
+    slot = hi | ((slot + 1) & wrap);
+  }
+  return kGslotFull;
+}
+// Linear probing wraps at the end of the table -- in partitioned mode at the end of the key's PARTITION SLICE
+// (cap >> part_lg slots, the slots whose index starts with the partition's bits), so that a key never sits outside
+// its partition's slice and the fold kernel, which holds one slice in shared memory, owns every slot a tuple of
+// its partition can reach.  A slice fills up like a small table of its own: keys / P of them land in it, +- a few
+// tens at 2048 slots, so the table's load factor decides, as before.
+__device__ __forceinline__ uint64_t g_probe_wrap(const DevTables& T) {
+  const uint64_t slice = T.part_lg ? T.cap >> T.part_lg : 0;
+  return (slice ? slice : T.cap) - 1;
+}
+
 // Find or claim the slot of (window, key).  Returns the slot inside the window's table, or
 // kGslotFull / kGslotWindow.  *ring_slot receives the window's ring index.
 __device__ __noinline__ uint32_t g_find_or_insert(const DevTables& T, uint64_t win, uint64_t kh, uint32_t* ring_slot) {
@@ -35,20 +61,10 @@ __device__ __noinline__ uint32_t g_find_or_insert(const DevTables& T, uint64_t w
     unsigned long long old = atomicCAS(&T.ring_win[r], (unsigned long long)kNoWindow, (unsigned long long)win);
     if (old != kNoWindow && old != win) return kGslotWindow;
   }
-  unsigned long long* keys = T.keys + (uint64_t)r * T.stride;
   if (kh >= kLockKey) return (uint32_t)T.cap + (uint32_t)(kh & 1);   // side slots for the sentinel-valued keys
-  uint32_t shift = 64u - ilog2_u64(T.cap);
-  uint64_t slot = (kh * kHashMul) >> shift;
-  for (uint64_t i = 0; i < T.cap; i++) {
-    unsigned long long k = keys[slot];
-    if (k == kh) return (uint32_t)slot;
-    if (k == kEmptyKey) {
-      unsigned long long old = atomicCAS(&keys[slot], (unsigned long long)kEmptyKey, (unsigned long long)kh);
-      if (old == kEmptyKey || old == kh) return (uint32_t)slot;
-    }
-    slot = (slot + 1) & (T.cap - 1);
-  }
-  return kGslotFull;
+  const uint32_t shift = 64u - ilog2_u64(T.cap);
+  const uint64_t wrap = g_probe_wrap(T);
+  return g_probe_from(T, r, kh, (kh * kHashMul) >> shift, wrap, wrap + 1);
 }
 
 __device__ __forceinline__ void g_update(const DevTables& T, uint32_t ops, uint64_t gi, unsigned long long cnt,
@@ -231,6 +247,29 @@ __device__ __forceinline__ void part_cursors_store(const DevTables& T) {
   for (uint32_t i = threadIdx.x; i < (1u << T.part_lg); i += blockDim.x) T.part_fill[((uint64_t)blockIdx.x << T.part_lg) + i] = min(cur[i], T.part_cap);
 }
 
+// one event's value into the shared-memory entry `slot`
+template <bool INTV>
+__device__ __forceinline__ void smem_apply(const SmemTable& M, int slot, uint32_t ops, double v, int32_t iv) {
+  atomicAdd(&M.cnt<INTV>()[slot], 1u);
+  if (INTV) {
+    if (ops & BH_OP_SUM) {
+      const uint32_t add = (uint32_t)iv;
+      const uint32_t old = atomicAdd(M.sum_lo() + slot, add);
+      const int32_t hi = (iv >> 31) + (int32_t)(old + add < old);   // sign extension + carry
+      if (hi) atomicAdd(M.sum_hi() + slot, hi);
+    }
+    if (ops & BH_OP_MIN) atomicMin(M.imin() + slot, iv);
+    if (ops & BH_OP_MAX) atomicMax(M.imax() + slot, iv);
+  } else {
+    const uint64_t ord = f64_order((uint64_t)__double_as_longlong(v));
+    if (ops & BH_OP_SUM) atomicAdd(M.fsum() + slot, v);
+    // both columns only ever grow: a plain read that already shows a value at least as large makes the
+    // (CAS-loop) atomic unnecessary, and after a key's first few events that is the usual case
+    if ((ops & BH_OP_MIN) && (unsigned long long)~ord > M.fmin_inv()[slot]) atomicMax(M.fmin_inv() + slot, (unsigned long long)~ord);
+    if ((ops & BH_OP_MAX) && (unsigned long long)ord > M.fmax_ord()[slot]) atomicMax(M.fmax_ord() + slot, (unsigned long long)ord);
+  }
+}
+
 // One event into the tables.  `wbase` is the CTA's first window minus one.
 // INTV: `iv` is the value; otherwise `v`.  `mask` = the lanes that call it together.
 // PART_OK = false (the drain kernel): a miss goes to the HBM table directly even in partitioned mode.
@@ -250,24 +289,7 @@ __device__ __forceinline__ void aggregate_event(const DevSchema& S, const DevTab
       uint64_t gi = (uint64_t)((uint32_t)win & (T.ring - 1)) * T.stride + gs;
       atomicAdd(&T.hist[gi * T.hist_buckets + hist_bucket((uint64_t)__double_as_longlong(v), T.hist_buckets, S.hist_e0)], 1u);
     }
-    atomicAdd(&M.cnt<INTV>()[slot], 1u);
-    if (INTV) {
-      if (ops & BH_OP_SUM) {
-        const uint32_t add = (uint32_t)iv;
-        const uint32_t old = atomicAdd(M.sum_lo() + slot, add);
-        const int32_t hi = (iv >> 31) + (int32_t)(old + add < old);   // sign extension + carry
-        if (hi) atomicAdd(M.sum_hi() + slot, hi);
-      }
-      if (ops & BH_OP_MIN) atomicMin(M.imin() + slot, iv);
-      if (ops & BH_OP_MAX) atomicMax(M.imax() + slot, iv);
-    } else {
-      const uint64_t ord = f64_order((uint64_t)__double_as_longlong(v));
-      if (ops & BH_OP_SUM) atomicAdd(M.fsum() + slot, v);
-      // both columns only ever grow: a plain read that already shows a value at least as large makes the
-      // (CAS-loop) atomic unnecessary, and after a key's first few events that is the usual case
-      if ((ops & BH_OP_MIN) && (unsigned long long)~ord > M.fmin_inv()[slot]) atomicMax(M.fmin_inv() + slot, (unsigned long long)~ord);
-      if ((ops & BH_OP_MAX) && (unsigned long long)ord > M.fmax_ord()[slot]) atomicMax(M.fmax_ord() + slot, (unsigned long long)ord);
-    }
+    smem_apply<INTV>(M, slot, ops, v, iv);
     C.ok++;
     return;
   }
@@ -1511,6 +1533,202 @@ k_part_drain(const __grid_constant__ DevSchema S, const __grid_constant__ DevTab
 }
 
 // =========================================================================================
+// partitioned mode, second phase, slice-mirror form: the fold used whenever a slice (or a power-of-two part of
+// it) fits shared memory
+// =========================================================================================
+// A partition's slots are one contiguous slice of every window's table and no key of the partition sits outside
+// it (g_probe_wrap), and while the fold runs nobody else touches it.  So the CTA that owns the partition does not
+// go through a hashed front table and per-entry HBM atomics at all: for each open window it loads the slice's KEY
+// column into shared memory (coalesced), probes and claims slots there exactly as g_find_or_insert would in HBM
+// (same home slot, same order), accumulates count / sum / min / max -- and the histogram rows, as 16-bit counters --
+// per SLOT in shared memory, and adds the touched rows back with plain coalesced read-modify-writes.  HBM traffic
+// per fold: the tuples once (16 B each), the key column of the open windows once, and 64 B (+ 2 x 4 B per live
+// bucket) per touched (key, window) -- not one random sector per tuple and table.
+// A slice larger than shared memory is taken in `sub`-slot parts; a tuple's probe chain that runs off the end of
+// the part in shared memory goes on in the HBM table (those slots are this CTA's too, and not in shared memory at
+// that moment).  Tuples are re-read once per (window, part) pass: after the first pass they come from L2.
+// 16-bit histogram counters cannot overflow: with histograms a pass takes regions holding <= 65 535 tuples together
+// (a "round"); a partition with more is folded in several rounds.
+__shared__ unsigned long long g_seen;
+__shared__ uint32_t g_round_end;
+
+template <bool INTV>
+__global__ void __launch_bounds__(kDrainThreads, 1)
+k_part_fold(const __grid_constant__ DevSchema S, const __grid_constant__ DevTables T, uint32_t sub_lg) {
+  const uint32_t ops = S.ops;
+  const bool hist = (ops & BH_OP_HIST) != 0;
+  const uint32_t B = T.hist_buckets, sub = 1u << sub_lg;
+  const SmemTable M = smem_table_carve<INTV>(sub, false);
+  uint8_t* after = g_smem + (((size_t)sub * smem_slot_bytes(INTV, false) + 15) & ~(size_t)15);
+  unsigned long long* ringwin = (unsigned long long*)after;
+  uint32_t* h32 = (uint32_t*)(after + (((size_t)T.ring * 8 + 15) & ~(size_t)15));     // u16 [sub][B], two to a word
+  const uint32_t hwords = hist ? (sub * B) / 2 : 0;
+  if (threadIdx.x < 8) g_cnt[threadIdx.x] = 0;
+  for (uint32_t r = threadIdx.x; r < T.ring; r += blockDim.x) ringwin[r] = T.ring_win[r];
+  __syncthreads();
+  unsigned long long open = 0;
+  for (uint32_t r = 0; r < T.ring; r++) if (ringwin[r] != kNoWindow) open |= 1ull << r;
+  const uint32_t P = 1u << T.part_lg, sh = 64u - T.part_lg, cap_sh = 64u - ilog2_u64(T.cap);
+  const uint32_t slice = (uint32_t)(T.cap >> T.part_lg), n_sub = slice >> sub_lg;
+  const uint32_t lane = threadIdx.x & 31;
+  const uint32_t ctas = min(T.part_ctas, kDrainMaxCtas);
+  volatile unsigned long long* vkey = M.key();
+  LaneCounters C{0u};
+  for (uint32_t p = blockIdx.x; p < P; p += gridDim.x) {
+    for (uint32_t c = threadIdx.x; c < ctas; c += blockDim.x) g_fill[c] = min(T.part_fill[((uint64_t)c << T.part_lg) | p], T.part_cap);
+    __syncthreads();
+    for (uint32_t c0 = 0; c0 < ctas;) {
+      if (threadIdx.x == 0) {
+        uint32_t c1 = ctas;
+        if (hist) { uint32_t sum = 0; c1 = c0; while (c1 < ctas && sum + g_fill[c1] <= 65535u) sum += g_fill[c1++]; if (c1 == c0) c1++; }
+        g_round_end = c1; g_seen = 0;
+      }
+      __syncthreads();
+      const uint32_t c1 = g_round_end;
+      bool first = true;                     // the round's first pass also notes which windows have tuples at all
+      unsigned long long todo = open;
+      for (uint32_t r = 0; r < T.ring; r++) {
+        for (uint32_t sb = 0; sb < n_sub && ((todo >> r) & 1); sb++) {
+          const uint64_t g0 = (uint64_t)r * T.stride + (uint64_t)p * slice + ((uint64_t)sb << sub_lg);
+          // ---- the part's key column in, everything else zero
+          for (uint32_t i = threadIdx.x; i < sub; i += blockDim.x) {
+            M.key()[i] = __ldcg(T.keys + g0 + i);
+            M.cnt<INTV>()[i] = 0;
+            if (INTV) { M.sum_lo()[i] = 0; M.sum_hi()[i] = 0; M.imin()[i] = 0x7FFFFFFF; M.imax()[i] = (int32_t)0x80000000; }
+            else { M.fsum()[i] = 0.0; M.fmin_inv()[i] = 0; M.fmax_ord()[i] = 0; }
+          }
+          for (uint32_t i = threadIdx.x; i < hwords; i += blockDim.x) h32[i] = 0;
+          if (threadIdx.x == 0) g_next = c0;
+          __syncthreads();
+          // ---- the round's tuples: warps take whole regions, 32 tuples at a time, the next 32 already in flight
+          {
+            auto grab = [&]() { uint32_t v = 0; if (lane == 0) v = atomicAdd(&g_next, 1u); return __shfl_sync(0xFFFFFFFFu, v, 0); };
+            // a region just taken is pulled into L2 whole (<= 128 B per tuple octet): the 32-tuple loads that follow
+            // then wait for L2, not for DRAM
+            auto next_pos = [&](uint32_t& c, uint32_t& i0) {
+              while (c < c1 && i0 >= g_fill[c]) {
+                c = grab(); i0 = 0;
+                if (c < c1) {
+                  const uint8_t* rb = (const uint8_t*)(T.part_tuples + (((uint64_t)c << T.part_lg) | p) * T.part_cap);
+                  for (uint32_t o = lane * 128u; o < g_fill[c] * 16u; o += 32u * 128u) prefetch_l2(rb + o);
+                }
+              }
+            };
+            auto load = [&](uint32_t c, uint32_t i0, bool& valid) {
+              uint4 t = make_uint4(0, 0, 0, 0);
+              valid = c < c1 && i0 + lane < g_fill[c];
+              if (valid) t = ldg_stream_here(T.part_tuples + (((uint64_t)c << T.part_lg) | p) * T.part_cap + i0 + lane);
+              return t;
+            };
+            unsigned long long seen = 0;
+            uint32_t c = grab(), i0 = 0;
+            next_pos(c, i0);
+            bool valid;
+            uint4 t = load(c, i0, valid);
+            while (c < c1) {
+              uint32_t nc = c, ni = i0 + 32;
+              next_pos(nc, ni);
+              bool nvalid;
+              const uint4 nt = load(nc, ni, nvalid);
+              const uint64_t a = ((uint64_t)t.y << 32) | t.x, vbits = ((uint64_t)t.w << 32) | t.z;
+              const uint32_t rr = (uint32_t)(a >> sh);
+              const uint64_t hs = (a & ((1ull << sh) - 1)) | ((uint64_t)p << sh);
+              const uint32_t off = (uint32_t)(hs >> cap_sh) & (slice - 1);
+              if (valid && first) {
+                seen |= 1ull << rr;
+                if (!((open >> rr) & 1)) C.bump(C_WINDOW);          // (its window is gone: cannot happen, a close folds first)
+              }
+              const bool mine = valid && rr == r && (off >> sub_lg) == sb;
+              const uint32_t mask = __ballot_sync(0xFFFFFFFFu, mine);
+              if (mine) {
+                const uint64_t kh = hs * kHashMulInv;
+                const double v = __longlong_as_double((long long)vbits);
+                uint32_t j = off & (sub - 1);
+                int slot = -1;
+                for (uint32_t left = n_sub == 1 ? sub : sub - j; left; left--) {
+                  unsigned long long k = vkey[j];
+                  if (k == kEmptyKey) {
+                    k = atomicCAS(&M.key()[j], (unsigned long long)kEmptyKey, (unsigned long long)kh);
+                    if (k == kEmptyKey) k = kh;
+                  }
+                  if (k == kh) { slot = (int)j; break; }
+                  j = (j + 1) & (sub - 1);
+                }
+                __syncwarp(mask);          // the lanes left the probe loop at different turns
+                if (slot >= 0) {
+                  smem_apply<INTV>(M, slot, ops, v, INTV ? (int32_t)v : 0);
+                  if (hist) {
+                    const uint32_t hi = (uint32_t)slot * B + hist_bucket(vbits, B, S.hist_e0);
+                    atomicAdd(&h32[hi >> 1], 1u << ((hi & 1u) * 16u));
+                  }
+                } else if (n_sub == 1) {
+                  C.bump(C_TABLE_FULL);
+                } else {
+                  // off the end of the part held here: the rest of the chain is walked in the HBM table
+                  const uint64_t start = (uint64_t)p * slice + ((((uint64_t)sb + 1) << sub_lg) & (slice - 1));
+                  const uint32_t gs = g_probe_from(T, r, kh, start, slice - 1, slice - sub);
+                  if (gs == kGslotFull) C.bump(C_TABLE_FULL);
+                  else {
+                    const uint64_t gi = (uint64_t)r * T.stride + gs, ord = f64_order(vbits);
+                    g_update(T, ops, gi, 1ull, v, ~ord, ord);
+                    if (hist) atomicAdd(&T.hist[gi * B + hist_bucket(vbits, B, S.hist_e0)], 1u);
+                  }
+                }
+              }
+              __syncwarp();
+              c = nc; i0 = ni; t = nt; valid = nvalid;
+            }
+            if (first) {
+              const uint32_t lo = __reduce_or_sync(0xFFFFFFFFu, (uint32_t)seen), hi = __reduce_or_sync(0xFFFFFFFFu, (uint32_t)(seen >> 32));
+              if (lane == 0 && (lo | hi)) atomicOr(&g_seen, ((unsigned long long)hi << 32) | lo);
+            }
+          }
+          __syncthreads();
+          // ---- touched rows back: coalesced read-modify-write, nobody else is in this slice
+          for (uint32_t i = threadIdx.x; i < sub; i += blockDim.x) {
+            const uint32_t cnt = M.cnt<INTV>()[i];
+            if (!cnt) continue;
+            __stcg(T.keys + g0 + i, M.key()[i]);
+            ulonglong2* sp = (ulonglong2*)(T.stats + g0 + i);
+            ulonglong2 s0 = __ldcg(sp), s1 = __ldcg(sp + 1);          // {count, sum} {min_inv, max_ord}
+            double sum; unsigned long long mn_inv, mx_ord;
+            if (INTV) {
+              sum = (double)(long long)(((unsigned long long)(uint32_t)M.sum_hi()[i] << 32) | M.sum_lo()[i]);
+              mn_inv = ~f64_order((uint64_t)__double_as_longlong((double)M.imin()[i]));
+              mx_ord = f64_order((uint64_t)__double_as_longlong((double)M.imax()[i]));
+            } else {
+              sum = M.fsum()[i]; mn_inv = M.fmin_inv()[i]; mx_ord = M.fmax_ord()[i];
+            }
+            s0.x += cnt;
+            if (ops & BH_OP_SUM) s0.y = (unsigned long long)__double_as_longlong(__longlong_as_double((long long)s0.y) + sum);
+            if (ops & BH_OP_MIN) s1.x = max(s1.x, mn_inv);
+            if (ops & BH_OP_MAX) s1.y = max(s1.y, mx_ord);
+            __stcg(sp, s0); __stcg(sp + 1, s1);
+          }
+          for (uint32_t i = threadIdx.x; i < hwords; i += blockDim.x) {
+            const uint32_t w = h32[i];
+            if (!w) continue;
+            uint32_t* g = T.hist + g0 * B + 2ull * i;
+            if (w & 0xFFFFu) __stcg(g, __ldcg(g) + (w & 0xFFFFu));
+            if (w >> 16) __stcg(g + 1, __ldcg(g + 1) + (w >> 16));
+          }
+          __syncthreads();
+          if (first) { todo &= g_seen; first = false; }
+        }
+      }
+      c0 = c1;
+    }
+    for (uint32_t cc = threadIdx.x; cc < T.part_ctas; cc += blockDim.x) T.part_fill[((uint64_t)cc << T.part_lg) | p] = 0;
+    __syncthreads();
+  }
+  // the tuples were counted as aggregated when they were logged: only what was refused now moves to the drop counters
+  if (threadIdx.x == C_TABLE_FULL || threadIdx.x == C_WINDOW) {
+    const unsigned long long d = g_cnt[threadIdx.x];
+    if (d) { atomicAdd(&T.counters[threadIdx.x], d); atomicAdd(&T.counters[C_OK], 0ull - d); }
+  }
+}
+
+// =========================================================================================
 // window close: export (compact by owner), merge, recycle
 // =========================================================================================
 // Liveness is decided from the key column (8 bytes per slot, streamed) so that a close or an export of a large,
@@ -1739,6 +1957,7 @@ cudaError_t configure_kernels(const LaunchGeom& G) {
                        (const void*)k_process_raw<true, false, 1>, (const void*)k_process_raw<true, false, 2>,
                        (const void*)k_decode<false>, (const void*)k_decode<true>, (const void*)k_process_columns,
                        (const void*)k_part_drain<true>, (const void*)k_part_drain<false>,
+                       (const void*)k_part_fold<true>, (const void*)k_part_fold<false>,
                        (const void*)k_verify_keys<false>, (const void*)k_verify_keys<true>};
   for (const void* f : fns) {
     cudaFuncAttributes at;
@@ -1862,10 +2081,36 @@ cudaError_t launch_process_columns(const DevSchema& S, const DevTables& T0, cons
 cudaError_t launch_part_drain(const DevSchema& S, const DevTables& T, const LaunchGeom& G, bool intv, cudaStream_t st, int* launches) {
   if (!T.part_lg) return cudaSuccess;
   const bool hist = (S.ops & BH_OP_HIST) != 0;
-  const size_t ring_bytes = (size_t)T.ring * 8;
-  const uint32_t ns = pick_smem_slots(intv, hist, G, ring_bytes + 2048);     // + the kernel's static arrays
-  const size_t smem = (((size_t)ns * smem_slot_bytes(intv, hist) + 15) & ~(size_t)15) + ring_bytes;
+  const size_t ring_bytes = ((size_t)T.ring * 8 + 15) & ~(size_t)15;
   const uint32_t grid = min((uint32_t)G.sms, 1u << T.part_lg);
+  // Which fold.  Measured on the many-key shapes (tools/foldbench.sh, ms per 12.5 M events, log + fold, hashed / mirror):
+  //   1 M keys, 2^21 slots:  f64 + hist 0.86 / 1.17   f64 0.63 / 0.72   int 0.55 / 0.66
+  //  10 M keys, 2^24 slots:  f64 + hist 2.44 / 4.07   f64 1.42 / 1.27   int 1.36 / 1.20
+  // The mirror pays one walk over the tuples per (window, part) pass and wins once a partition's keys no longer
+  // fit the hashed front table (4096 slots), where the hashed fold degrades to one HBM update per tuple; with
+  // histograms its parts are 1024 slots and the passes cost more than they save.
+  // BEHOLDER_FOLD=0 / 1 forces one of them, BEHOLDER_FOLD_SUB_LG caps the part size (tests, experiments).
+  const char* e_fold = getenv("BEHOLDER_FOLD");
+  const char* e_sub = getenv("BEHOLDER_FOLD_SUB_LG");
+  const uint64_t slice = T.cap >> T.part_lg;
+  const int fold_on = e_fold ? atoi(e_fold) : (!hist && slice >= 8192);
+  const int fold_sub_lg_max = e_sub ? atoi(e_sub) : 30;
+  if (fold_on && slice >= 64 && T.ring <= 64 && (!hist || T.part_cap <= 65535u)) {
+    const size_t per_slot = smem_slot_bytes(intv, false) + (hist ? 2u * T.hist_buckets : 0u);
+    uint32_t sub_lg = 0;
+    while ((2ull << sub_lg) <= slice && (int)sub_lg + 1 <= fold_sub_lg_max &&
+           (2ull << sub_lg) * per_slot + 16 + ring_bytes + 2048 <= (size_t)G.smem_optin) sub_lg++;
+    if (sub_lg >= 6) {
+      const size_t sub = (size_t)1 << sub_lg;
+      const size_t smem = ((sub * smem_slot_bytes(intv, false) + 15) & ~(size_t)15) + ring_bytes + (hist ? sub * T.hist_buckets * 2 : 0);
+      if (intv) k_part_fold<true><<<grid, kDrainThreads, smem, st>>>(S, T, sub_lg);
+      else k_part_fold<false><<<grid, kDrainThreads, smem, st>>>(S, T, sub_lg);
+      if (launches) (*launches)++;
+      return cudaGetLastError();
+    }
+  }
+  const uint32_t ns = pick_smem_slots(intv, hist, G, (size_t)T.ring * 8 + 2048);     // + the kernel's static arrays
+  const size_t smem = (((size_t)ns * smem_slot_bytes(intv, hist) + 15) & ~(size_t)15) + (size_t)T.ring * 8;
   if (intv) k_part_drain<true><<<grid, kDrainThreads, smem, st>>>(S, T, ns);
   else k_part_drain<false><<<grid, kDrainThreads, smem, st>>>(S, T, ns);
   if (launches) (*launches)++;

@@ -74,6 +74,29 @@ def test_single_event_entries_logged_at_the_flush_under_every_op_subset(ops, f64
     _check(spec, 2, 600_000, ops, 1 << 20, threads=16)
 
 
+@pytest.mark.parametrize("sub_lg", ["30", "7"])
+@pytest.mark.parametrize("f64", [False, True])
+def test_slice_mirror_fold_forced(monkeypatch, f64, sub_lg):
+    # the fold that holds a partition's slice of the table in shared memory (by itself it is used from 8192-slot
+    # slices on): whole slices, and 128-slot parts of 256-slot slices so that probe chains run off the part held in
+    # shared memory and go on in the HBM table; with histograms (16-bit counters, several rounds per partition)
+    monkeypatch.setenv("BEHOLDER_FOLD", "1")
+    monkeypatch.setenv("BEHOLDER_FOLD_SUB_LG", sub_lg)
+    spec = SynthSpec(n_keys=20_000, rate_per_ms=200, value_f64=f64, value_signed=f64, malformed_ppm=3000, unknown_enum_ppm=3000)
+    k = _check(spec, 3, 1_500_000, ALL_OPS | (L.OP_HIST if f64 else 0), 1 << 16, reads_between=True, threads=16)
+    assert k["smem_spills"] > 1_000_000
+    # a well filled table (load 0.73, 256-slot slices holding 188 +- 14 keys): long chains, wrapping inside the slices
+    spec = SynthSpec(n_keys=6_000, rate_per_ms=200, zipf=True, value_f64=f64)
+    _check(spec, 2, 1_000_000, ALL_OPS, 1 << 13, threads=8)
+
+
+def test_slice_mirror_fold_at_the_size_that_selects_it():
+    # 2^24 slots -> 2048 partitions of 8192 slots, folded in two 4096-slot parts; 3 M keys, ~2 events per key
+    spec = SynthSpec(n_keys=3_000_000, rate_per_ms=1000)
+    k = _check(spec, 2, 3_000_000, ALL_OPS, 1 << 24, flags=0, ring=4)
+    assert k["smem_spills"] > 4_000_000
+
+
 def test_partitioning_is_on_by_itself_for_large_tables_and_can_be_kept_off():
     spec = SynthSpec(n_keys=100_000, rate_per_ms=400)
     k_on = _check(spec, 1, 2_000_000, ALL_OPS, 1 << 18, flags=0, threads=16)
