@@ -67,13 +67,25 @@ __device__ __noinline__ uint32_t g_find_or_insert(const DevTables& T, uint64_t w
   return g_probe_from(T, r, kh, (kh * kHashMul) >> shift, wrap, wrap + 1);
 }
 
+// LOOK = true: the min / max atomics are skipped when a plain read already shows a value at least as good -- right for
+// events going to the table one by one (a key's row settles after its first few events and then costs two L2 reads,
+// no atomics).  LOOK = false: four fire-and-forget reductions, nothing to wait for -- right where a row is met once
+// per launch (the shared-table flush, the merge of exported rows): there the reads were two more round trips per row.
+template <bool LOOK = true>
 __device__ __forceinline__ void g_update(const DevTables& T, uint32_t ops, uint64_t gi, unsigned long long cnt,
                                          double sum, unsigned long long min_inv, unsigned long long max_ord) {
   Stat* s = T.stats + gi;
   atomicAdd(&s->count, cnt);
   if (ops & BH_OP_SUM) atomicAdd(&s->sum, sum);
-  if ((ops & BH_OP_MIN) && min_inv > s->min_inv) atomicMax(&s->min_inv, min_inv);
-  if ((ops & BH_OP_MAX) && max_ord > s->max_ord) atomicMax(&s->max_ord, max_ord);
+  if ((ops & BH_OP_MIN) && (!LOOK || min_inv > s->min_inv)) atomicMax(&s->min_inv, min_inv);
+  if ((ops & BH_OP_MAX) && (!LOOK || max_ord > s->max_ord)) atomicMax(&s->max_ord, max_ord);
+}
+// shared-memory fetch-and-add by shared-window address (a file-scope __shared__ counter reached through a lambda's
+// reference capture is otherwise treated as a generic address: a slower, long-scoreboard atomic)
+__device__ __forceinline__ uint32_t atoms_add(uint32_t* p, uint32_t v) {
+  uint32_t old;
+  asm volatile("atom.shared.add.u32 %0, [%1], %2;" : "=r"(old) : "r"((uint32_t)__cvta_generic_to_shared(p)), "r"(v) : "memory");
+  return old;
 }
 
 // =========================================================================================
@@ -354,7 +366,7 @@ __device__ __forceinline__ void smem_table_flush(const DevSchema& S, const DevTa
     } else {
       sum = M.fsum()[i]; mn_inv = M.fmin_inv()[i]; mx_ord = M.fmax_ord()[i];
     }
-    g_update(T, S.ops, (uint64_t)r * T.stride + gs, c, sum, mn_inv, mx_ord);
+    g_update<false>(T, S.ops, (uint64_t)r * T.stride + gs, c, sum, mn_inv, mx_ord);
   }
 }
 
@@ -1490,7 +1502,7 @@ k_part_drain(const __grid_constant__ DevSchema S, const __grid_constant__ DevTab
       __syncthreads();
       // Warps take whole regions, handed out by a shared counter (regions differ in fill), 32 tuples at a time;
       // the next 32 are already in flight while the current ones are aggregated.
-      auto grab = [&]() { uint32_t v = 0; if (lane == 0) v = atomicAdd(&g_next, 1u); return __shfl_sync(0xFFFFFFFFu, v, 0); };
+      auto grab = [&]() { uint32_t v = 0; if (lane == 0) v = atoms_add(&g_next, 1u); return __shfl_sync(0xFFFFFFFFu, v, 0); };
       auto next_pos = [&](uint32_t& c, uint32_t& i0) { while (c < ctas && i0 >= g_fill[c]) { c = grab(); i0 = 0; } };
       auto load = [&](uint32_t c, uint32_t i0, bool& valid) {
         uint4 t = make_uint4(0, 0, 0, 0);
@@ -1602,7 +1614,7 @@ k_part_fold(const __grid_constant__ DevSchema S, const __grid_constant__ DevTabl
           __syncthreads();
           // ---- the round's tuples: warps take whole regions, 32 tuples at a time, the next 32 already in flight
           {
-            auto grab = [&]() { uint32_t v = 0; if (lane == 0) v = atomicAdd(&g_next, 1u); return __shfl_sync(0xFFFFFFFFu, v, 0); };
+            auto grab = [&]() { uint32_t v = 0; if (lane == 0) v = atoms_add(&g_next, 1u); return __shfl_sync(0xFFFFFFFFu, v, 0); };
             // a region just taken is pulled into L2 whole (<= 128 B per tuple octet): the 32-tuple loads that follow
             // then wait for L2, not for DRAM
             auto next_pos = [&](uint32_t& c, uint32_t& i0) {
@@ -1858,7 +1870,7 @@ __global__ void k_merge(const __grid_constant__ DevSchema S, const __grid_consta
     uint64_t gi = (uint64_t)r * T.stride + gs;
     uint64_t omin = f64_order((uint64_t)__double_as_longlong(rec.min));
     uint64_t omax = f64_order((uint64_t)__double_as_longlong(rec.max));
-    g_update(T, S.ops, gi, rec.count, rec.sum, ~omin, omax);
+    g_update<false>(T, S.ops, gi, rec.count, rec.sum, ~omin, omax);
     if (hist && T.hist)
       for (uint32_t b = 0; b < T.hist_buckets; b++) {
         uint32_t h = hist[i * T.hist_buckets + b];
@@ -1893,7 +1905,7 @@ __global__ void k_merge_blocks(const __grid_constant__ DevSchema S, const __grid
       const uint64_t gi = (uint64_t)r * T.stride + gs;
       const uint64_t omin = f64_order((uint64_t)__double_as_longlong(rec.min));
       const uint64_t omax = f64_order((uint64_t)__double_as_longlong(rec.max));
-      g_update(T, S.ops, gi, rec.count, rec.sum, ~omin, omax);
+      g_update<false>(T, S.ops, gi, rec.count, rec.sum, ~omin, omax);
       if (hist && T.hist)
         for (uint32_t k = 0; k < T.hist_buckets; k++) {
           const uint32_t h = __ldcg(&hist[row * T.hist_buckets + k]);
