@@ -47,6 +47,10 @@ open(f"{P}/{R}_fused_k_process_raw_ncu_full.txt", "w").write(
 open(f"{P}/{R}_k_part_drain_ncu_full.txt", "w").write(
     kernel_summary(f"{G}/{R}_drain.ncu-rep", "k_part_drain<0>: fold of the tuple log, C3 shape (1 M keys, histograms, f64; tools/c3bench.py --slabs 12)",
                    1, "launch", 16))
+if os.path.exists(f"{G}/{R}_fold.ncu-rep"):
+    open(f"{P}/{R}_k_part_fold_ncu_full.txt", "w").write(
+        kernel_summary(f"{G}/{R}_fold.ncu-rep", "k_part_fold<1>: slice-mirror fold of the tuple log, C4 shape on one GPU (10 M keys, 2^24 slots, int32, no histograms; tools/c3bench.py --slabs 12 --int --no-hist --keys 10000000)",
+                       1, "launch", 16))
 for f in (f"{R}_launch_list_summary.txt", f"{R}_launches.csv"):
     open(f"{P}/{f}", "w").write(open(f"{G}/{f}").read())
 
