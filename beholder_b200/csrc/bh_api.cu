@@ -500,8 +500,8 @@ int bh_create(const bh_config* cfg, bh_ctx** out) {
   // partitioned (deferred) aggregation: on request, or by itself once a window's table is too large for L2
   const bool part = cfg->mode == BH_MODE_WINDOWED && !(cfg->flags & BH_F_NO_PARTITION) &&
                     ((cfg->flags & BH_F_PARTITIONED) || cap >= (1ull << 18));
+  uint32_t lg = 0;                                               // log2(partitions); 0 = not partitioned
   if (part) {
-    uint32_t lg = 0;
     while ((1ull << lg) < cap) lg++;
     // ~2048 table slots per partition, 64 .. 2048 partitions (at 2^24 slots 4 096 partitions are 5 % slower than
     // 1 024 or 2 048: the scatter of the log phase pays for every extra open region).  Measured at the C3 shape (2^21 slots): 512 / 1024 /
@@ -510,13 +510,21 @@ int bh_create(const bh_config* cfg, bh_ctx** out) {
     // fewer crowd the fold's shared table.
     lg = lg > 22 ? 11 : (lg < 17 ? 6 : lg - 11);
     if (const char* e = getenv("BEHOLDER_PART_LG")) { int v = atoi(e); if (v >= 4 && v <= 14) lg = (uint32_t)v; }   // experiments
+    while ((1u << lg) < ring) lg++;                              // a tuple carries its ring slot in the partition bits
     // probing wraps inside a partition's slice (g_probe_wrap): keep slices large enough to fill like the table
-    // does (256 slots: +- 8 keys around the mean)
+    // does (256 slots: +- 8 keys around the mean) -- fewer partitions for small tables, none if that cannot be
     uint32_t lgcap = 0;
     while ((1ull << lgcap) < cap) lgcap++;
-    if (lgcap < lg + 8) lg = lgcap - 8;                          // (cap >= 64 was checked; small forced tables only)
-    if (lgcap < 8 || (1u << lg) < ring || lg < 1)                // a tuple carries its ring slot in the partition bits
-      return fail(nullptr, BH_ERR_INVALID, "BH_F_PARTITIONED needs table_capacity >= 256 x max(2, window_ring) slots");
+    if (lgcap < lg + 8) {
+      const uint32_t lg2 = lgcap >= 8 ? lgcap - 8 : 0;
+      if (lg2 >= 1 && (1u << lg2) >= ring) lg = lg2;
+      else if (cfg->flags & BH_F_PARTITIONED) {
+        fail(c, BH_ERR_INVALID, "BH_F_PARTITIONED needs table_capacity >= 256 x max(2, window_ring) slots");
+        return bail(BH_ERR_INVALID);
+      } else lg = 0;
+    }
+  }
+  if (lg) {
     T.part_lg = lg;
     // regions x tuples stays constant: 2^20 tuples per SM = 16 MB, 2.5 GB of log on 148 SMs, ~93 M events per fold
     T.part_cap = cfg->part_region_tuples ? cfg->part_region_tuples : std::max(128u, (1u << 20) >> lg);

@@ -107,7 +107,12 @@ enum {
                                 * event.  Same results.  On by itself when table_capacity >= 2^18; this flag forces it
                                 * for smaller tables, BH_F_NO_PARTITION keeps it off.  While it is on, launches that feed
                                 * one context must be issued on one stream at a time (the library re-orders itself
-                                * across a change of stream), and reads (snapshot, export, counters) fold the log first. */
+                                * across a change of stream), and reads (snapshot, export, counters) fold the log first.
+                                * While it is on, a key's table slot is probed for inside its partition's slice of the
+                                * table only (table_capacity / partitions slots, kept >= 256), so dropped_table_full can
+                                * start a little before the whole table is full: size table_capacity for a load factor
+                                * <= 0.75 as for any open-addressing table.  Forcing it needs
+                                * table_capacity >= 256 x max(2, window_ring) (BH_ERR_INVALID otherwise). */
   BH_F_NO_PARTITION = 8,
   BH_F_VERIFY_KEYS = 16,       /* Full-key identity (collisions are detected, never silently merged).
                                 * Rows are identified by the 64-bit hash of their key; with this flag every raw batch is

@@ -97,6 +97,16 @@ def test_slice_mirror_fold_at_the_size_that_selects_it():
     assert k["smem_spills"] > 4_000_000
 
 
+def test_forcing_it_on_a_table_too_small_for_256_slot_slices_is_refused():
+    for cap, ring in ((256, 4), (512, 4), (4096, 32)):
+        with pytest.raises(bh.BeholderError) as e:
+            bh.Aggregator(bh.telemetry_progress(), mode=L.MODE_WINDOWED, key=KEY, ops=ALL_OPS, table_capacity=cap,
+                          window_ring=ring, flags=L.F_PARTITIONED)
+        assert e.value.code == L.BH_ERR_INVALID
+    bh.Aggregator(bh.telemetry_progress(), mode=L.MODE_WINDOWED, key=KEY, ops=ALL_OPS, table_capacity=1024, window_ring=4,
+                  flags=L.F_PARTITIONED).close()
+
+
 def test_partitioning_is_on_by_itself_for_large_tables_and_can_be_kept_off():
     spec = SynthSpec(n_keys=100_000, rate_per_ms=400)
     k_on = _check(spec, 1, 2_000_000, ALL_OPS, 1 << 18, flags=0, threads=16)
