@@ -738,13 +738,15 @@ __device__ __forceinline__ bool decode_fast(const DevSchema& S, const SmemRd& r,
 // the run-time schema is exactly this one; every other schema runs the same code on the DevSchema itself.
 // REF = false: the windowed grouping above.  REF = true: the reference's literal counter (BH_MODE_REFERENCE:
 // key = status, no key parts, no windows; mediaId is just another string to skip).
-template <bool REF>
+// F64 = true: the same message with `progress` declared double (BASELINE.json config 3's value type): field 3 is a
+// 64-bit wire value (tag 0x19) and the f64 shared table is used.
+template <bool REF, bool F64 = false>
 struct ProgressSchemaT {
   const DevSchema& dyn;
   __device__ __forceinline__ operator const DevSchema&() const { return dyn; }
   static constexpr uint32_t kFld1 = REF ? (uint32_t)BH_K_STRING : (BH_K_STRING | (BH_R_KEY << 8) | (1u << 16));
   static constexpr uint32_t kFld2 = REF ? (BH_K_INT32 | (BH_R_STATUS << 8)) : (BH_K_INT32 | ((BH_R_KEY | BH_R_STATUS) << 8) | (2u << 16));
-  static constexpr uint32_t kFld3 = BH_K_INT32 | (BH_R_VALUE << 8);
+  static constexpr uint32_t kFld3 = (F64 ? BH_K_DOUBLE : BH_K_INT32) | (BH_R_VALUE << 8);
   static constexpr uint32_t kFld4 = BH_K_STRING;
   __host__ __device__ static constexpr uint32_t field(uint32_t n) {
     return n == 1 ? kFld1 : n == 2 ? kFld2 : n == 3 ? kFld3 : n == 4 ? kFld4 : 0u;
@@ -753,9 +755,9 @@ struct ProgressSchemaT {
   __host__ __device__ static constexpr uint32_t part_fld(int k) { return REF ? 0u : k == 0 ? 1u : k == 1 ? 2u : 0u; }
   static constexpr uint32_t n_parts = REF ? 0 : 2, identity_key = 0, status_part = REF ? 1 : 0, has_enum = 1;
   static constexpr uint32_t has_window = REF ? 0 : 1, mode = REF ? BH_MODE_REFERENCE : BH_MODE_WINDOWED;
-  static constexpr uint32_t int_values = 1, fast_key0 = REF ? 0xFFFFFFFFu : 1u, fast_status = 2;
+  static constexpr uint32_t int_values = F64 ? 0 : 1, fast_key0 = REF ? 0xFFFFFFFFu : 1u, fast_status = 2;
   static constexpr uint32_t fast_status_part = REF ? 0 : 2, fast_value = 3;
-  static constexpr uint32_t fast_value_f64 = 0, tag_key0 = REF ? 0xFFFFFFFFu : 0x0Au, tag_status = 0x10, tag_value = 0x18;
+  static constexpr uint32_t fast_value_f64 = F64 ? 1 : 0, tag_key0 = REF ? 0xFFFFFFFFu : 0x0Au, tag_status = 0x10, tag_value = F64 ? 0x19 : 0x18;
   static constexpr uint32_t skip_str_mask = REF ? ((1u << 1) | (1u << 4)) : (1u << 4), skip_unk_mask = 0xFFFFu & ~0x1Eu;
   // run-time items
   uint32_t ops, pay_lo, pay_hi; uint64_t enum_mask, hash_seed, hash_mask, window_ms; Div64 wdiv;
@@ -765,9 +767,9 @@ struct ProgressSchemaT {
 };
 typedef ProgressSchemaT<false> ProgressSchema;
 
-template <bool REF>
+template <bool REF, bool F64 = false>
 static bool schema_matches(const DevSchema& S) {
-  typedef ProgressSchemaT<REF> P;
+  typedef ProgressSchemaT<REF, F64> P;
   for (uint32_t n = 0; n < 32; n++) if (S.fld[n] != P::field(n)) return false;
   for (int k = 0; k < BH_MAX_KEY_PARTS; k++) if (S.part_is_len[k] != P::part_len(k) || S.part_field[k] != P::part_fld(k)) return false;
   return S.n_parts == P::n_parts && S.identity_key == P::identity_key && S.status_part == P::status_part &&
@@ -777,8 +779,10 @@ static bool schema_matches(const DevSchema& S) {
          S.tag_status == P::tag_status && S.tag_value == P::tag_value && S.skip_str_mask == P::skip_str_mask &&
          S.skip_unk_mask == P::skip_unk_mask && S.mode == P::mode;
 }
-// 0 = no compiled-in view fits, 1 = windowed (mediaId, status) grouping, 2 = reference mode
-int progress_schema_variant(const DevSchema& S) { return schema_matches<false>(S) ? 1 : schema_matches<true>(S) ? 2 : 0; }
+// 0 = no compiled-in view fits, 1 = windowed (mediaId, status) grouping, 2 = reference mode, 3 = windowed with a double `progress`
+int progress_schema_variant(const DevSchema& S) {
+  return schema_matches<false>(S) ? 1 : schema_matches<true>(S) ? 2 : schema_matches<false, true>(S) ? 3 : 0;
+}
 bool progress_schema_matches(const DevSchema& S) { return progress_schema_variant(S) != 0; }
 
 template <class SC>
@@ -1327,7 +1331,7 @@ k_process_raw(const __grid_constant__ DevSchema S, const __grid_constant__ DevTa
   uint64_t wbase = 0;
   if (cs < ce) {
     if constexpr (PROG != 0) {
-      const ProgressSchemaT<PROG == 2> PS(S);
+      const ProgressSchemaT<PROG == 2, PROG == 3> PS(S);
       process_chunk<INTV, BIG>(PS, T, M, payload, offsets, ts, cs, ce, wb, C, wbase);
     } else {
       process_chunk<INTV, BIG>(S, T, M, payload, offsets, ts, cs, ce, wb, C, wbase);
@@ -2022,6 +2026,7 @@ cudaError_t configure_kernels(const LaunchGeom& G) {
                        (const void*)k_process_raw<false, false, 0>, (const void*)k_process_raw<false, true, 0>,
                        (const void*)k_process_raw<false, false, 0, kRawThreadsF64>, (const void*)k_process_raw<false, true, 0, kRawThreadsF64>,
                        (const void*)k_process_raw<true, false, 1>, (const void*)k_process_raw<true, false, 2>,
+                       (const void*)k_process_raw<false, false, 3>, (const void*)k_process_raw<false, false, 3, kRawThreadsF64>,
                        (const void*)k_decode<false>, (const void*)k_decode<true>, (const void*)k_process_columns,
                        (const void*)k_part_drain<true>, (const void*)k_part_drain<false>,
                        (const void*)k_part_fold<true>, (const void*)k_part_fold<false>,
@@ -2084,9 +2089,11 @@ cudaError_t launch_process_raw(const DevSchema& S0, const DevTables& T0, const L
   chunk = (chunk + 31u) & ~31u;
   const bool big = big_override < 0 ? S.big_messages != 0 : big_override != 0;
   // the reference's own schema (small messages, integer values): the kernel with the schema folded in
-  const int prog = intv && !big && !G.generic_only ? progress_schema_variant(S) : 0;
+  const int prog = !big && !G.generic_only ? progress_schema_variant(S) : 0;
   if (prog == 1) k_process_raw<true, false, 1><<<grid, kRawThreads, smem, st>>>(S, T, payload, offsets, ts, n, chunk, ns);
   else if (prog == 2) k_process_raw<true, false, 2><<<grid, kRawThreads, smem, st>>>(S, T, payload, offsets, ts, n, chunk, ns);
+  else if (prog == 3 && threads == kRawThreads) k_process_raw<false, false, 3><<<grid, threads, smem, st>>>(S, T, payload, offsets, ts, n, chunk, ns);
+  else if (prog == 3) k_process_raw<false, false, 3, kRawThreadsF64><<<grid, threads, smem, st>>>(S, T, payload, offsets, ts, n, chunk, ns);
   else if (intv && !big) k_process_raw<true, false, 0><<<grid, kRawThreads, smem, st>>>(S, T, payload, offsets, ts, n, chunk, ns);
   else if (intv) k_process_raw<true, true, 0><<<grid, kRawThreads, smem, st>>>(S, T, payload, offsets, ts, n, chunk, ns);
   else if (!big && threads == kRawThreads) k_process_raw<false, false, 0><<<grid, threads, smem, st>>>(S, T, payload, offsets, ts, n, chunk, ns);
