@@ -2173,7 +2173,9 @@ cudaError_t launch_part_drain(const DevSchema& S, const DevTables& T, const Laun
   const char* e_fold = getenv("BEHOLDER_FOLD");
   const char* e_sub = getenv("BEHOLDER_FOLD_SUB_LG");
   const uint64_t slice = T.cap >> T.part_lg;
-  const int fold_on = e_fold ? atoi(e_fold) : (!hist && slice >= 8192);
+  // (slices above 16 384 slots would be walked in 8 and more parts, one pass over the tuples each: not measured, left
+  // to the hashed fold)
+  const int fold_on = e_fold ? atoi(e_fold) : (!hist && slice >= 8192 && slice <= 16384);
   const int fold_sub_lg_max = e_sub ? atoi(e_sub) : 30;
   if (fold_on && slice >= 64 && T.ring <= 64 && (!hist || T.part_cap <= 65535u)) {
     const size_t per_slot = smem_slot_bytes(intv, false) + (hist ? 2u * T.hist_buckets : 0u);
